@@ -1,0 +1,445 @@
+// engine.cu -- see engine.cuh.
+#include "engine.cuh"
+#include "ops.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace fvad {
+
+namespace {
+
+// FFT.freqToBin, reference src/FFT.zig:140-167 (f32 arithmetic)
+int freq_to_bin(float freq, size_t sample_rate, size_t n_fft) {
+    const float nyq = (float)sample_rate / 2;
+    if (freq > nyq) throw Error(FVAD_ERR_OUT_OF_RANGE, "speech band above Nyquist");
+    if (freq < 0) throw Error(FVAD_ERR_NEGATIVE_FREQUENCY, "negative speech band frequency");
+    return (int)roundf(freq / ((float)sample_rate / (float)n_fft));
+}
+
+__global__ void init_scan_kernel(ScanState *states, double *rings, const ScanMachine *machines, int S, int M, int pitch) {
+    const int t = blockIdx.x;  // (stream, machine)
+    if (t >= S * M) return;
+    const ScanMachine mc = machines[t % M];
+    double *ring = rings + (size_t)t * pitch;
+    for (int i = threadIdx.x; i < pitch; i += blockDim.x) ring[i] = (mc.has_init && i < mc.n_long) ? mc.init_avg : 0.0;
+    if (threadIdx.x == 0) {
+        ScanState st;
+        memset(&st, 0, sizeof(st));
+        if (mc.has_init) {
+            // RollingAverage.init pre-fill (reference src/structures/RollingAverage.zig:19-25):
+            // written_count = len and last_avg = sum_i init*(1/len), accumulated sequentially in f64
+            st.long_cnt = mc.n_long;
+            const double scalar = 1.0 / (double)mc.n_long;
+            double acc = 0.0, sum = 0.0;
+            for (int i = 0; i < mc.n_long; ++i) { acc += mc.init_avg * scalar; sum += mc.init_avg; }
+            st.last_avg = acc;
+            st.long_sum = sum;
+            st.has_last = 1;
+        }
+        states[t] = st;
+    }
+}
+
+}  // namespace
+
+void Batch::init_machines(const fvad_config &cfg) {
+    const fvad_vad_config &vc = cfg.vad_config;
+    M_ = 1 + (int)(vc.alt_vad_machine_configs ? vc.n_alt_vad_machine_configs : 0);
+    machines_.resize((size_t)M_);
+    std::vector<int> lo, hi;
+    const float sr_f = (float)sample_rate_, fft_f = (float)fft_size_;
+    for (int m = 0; m < M_; ++m) {
+        const fvad_vad_machine_config &c = m ? vc.alt_vad_machine_configs[m - 1] : vc.vad_machine_config;
+        MachineDerived md;
+        memset(&md, 0, sizeof(md));
+        md.bin_lo = freq_to_bin(c.speech_min_freq, sample_rate_, (size_t)fft_size_);
+        md.bin_hi = freq_to_bin(c.speech_max_freq, sample_rate_, (size_t)fft_size_);
+        int b = -1;
+        for (size_t i = 0; i < lo.size(); ++i)
+            if (lo[i] == md.bin_lo && hi[i] == md.bin_hi) b = (int)i;
+        if (b < 0) { b = (int)lo.size(); lo.push_back(md.bin_lo); hi.push_back(md.bin_hi); }
+        ScanMachine &d = md.dev;
+        d.band = b;
+        // VADMachine.init, reference src/AudioPipeline/VADMachine.zig:75-106 (f32 products, truncation)
+        const float evals = sr_f / fft_f;
+        d.n_long = std::max<long long>(1, (long long)(evals * c.long_term_speech_avg_sec));
+        d.n_short = std::max<long long>(1, (long long)(evals * c.short_term_speech_avg_sec));
+        d.n_ratio = std::max<long long>(1, (long long)(evals * c.channel_vol_ratio_avg_sec));  // reference: no max(1); 0 would trap
+        d.has_init = c.has_initial_long_term_avg;
+        d.init_avg = c.initial_long_term_avg;
+        d.threshold_factor = (double)c.speech_threshold_factor;
+        d.ratio_threshold = (double)c.channel_vol_ratio_threshold;
+        // VADMachine.run :160-163, getOffsetRecording{Start,End} :312-325
+        d.min_to_open = (unsigned long long)(sr_f * c.min_consecutive_sec_to_open);
+        d.max_gap = (unsigned long long)(sr_f * c.max_speech_gap_sec);
+        d.start_margin = d.end_margin = (unsigned long long)(sr_f * 2);
+        d.min_duration_sec = c.min_vad_duration_sec;
+        d.frame_sec = fft_f / sr_f;  // trackSpeechStats :248-249
+        d.sample_rate_f = sr_f;
+        machines_[(size_t)m] = md;
+        ring_pitch_ = std::max(ring_pitch_, d.n_long + d.n_short + d.n_ratio);
+    }
+    n_bands_ = (int)lo.size();
+    band_lo_.ensure(lo.size());
+    band_hi_.ensure(hi.size());
+    FVAD_CUDA_CHECK(cudaMemcpy(band_lo_.p, lo.data(), lo.size() * sizeof(int), cudaMemcpyHostToDevice));
+    FVAD_CUDA_CHECK(cudaMemcpy(band_hi_.p, hi.data(), hi.size() * sizeof(int), cudaMemcpyHostToDevice));
+    std::vector<ScanMachine> dm((size_t)M_);
+    for (int m = 0; m < M_; ++m) dm[(size_t)m] = machines_[(size_t)m].dev;
+    d_machines_.ensure((size_t)M_);
+    FVAD_CUDA_CHECK(cudaMemcpy(d_machines_.p, dm.data(), dm.size() * sizeof(ScanMachine), cudaMemcpyHostToDevice));
+    const size_t SM = (size_t)S_ * M_;
+    d_states_.ensure(SM);
+    rings_.ensure(SM * (size_t)ring_pitch_);
+    max_segments_ = (SM > 64) ? 1024 : 4096;
+    d_segments_.ensure(SM * (size_t)max_segments_);
+    init_scan_kernel<<<(unsigned)SM, 128, 0, stream_>>>(d_states_.p, rings_.p, d_machines_.p, S_, M_, ring_pitch_);
+    FVAD_LAUNCHED();
+    FVAD_CUDA_CHECK(cudaGetLastError());
+    h_states_.assign(SM, ScanState{});
+    h_segments_.resize(SM * (size_t)max_segments_);
+}
+
+Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weights, const fvad_batch_options &opt)
+    : S_((int)n_streams), C_((int)cfg.n_channels), SC_((int)(n_streams * cfg.n_channels)),
+      sample_rate_(cfg.sample_rate), opt_(opt) {
+    // VADPipeline.init rejects anything but 48 kHz (reference VADPipeline.zig:55-58).  Documented
+    // deviation: 16 kHz is also accepted, as the same code with downsample rate 1.
+    if (sample_rate_ != 48000 && sample_rate_ != 16000)
+        throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "sample_rate must be 48000 (or 16000, documented deviation)");
+    if (S_ <= 0 || C_ <= 0) throw Error(FVAD_ERR_INVALID_ARGUMENT, "n_streams and n_channels must be positive");
+    fft_size_ = (int)cfg.vad_config.fft_size;
+    if (fft_size_ != 1024) throw Error(FVAD_ERR_INVALID_FFT_SIZE, "vad_config.fft_size: the GPU path implements 1024");
+    D_ = (int)(sample_rate_ / 16000);
+    skip_ = cfg.skip_processing != 0;
+    chunk_ = kChunk16 * D_;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        throw Error(FVAD_ERR_NO_DEVICE, "no CUDA device: libfvad_cuda has no CPU path");
+    if (opt_.device < 0 || opt_.device >= ndev) throw Error(FVAD_ERR_INVALID_ARGUMENT, "bad device ordinal");
+    FVAD_CUDA_CHECK(cudaSetDevice(opt_.device));
+    FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    for (auto &e : ev_) FVAD_CUDA_CHECK(cudaEventCreate(&e));
+    tables_.build();
+    launches0_ = g_kernel_launches;
+
+    // span size: bounded by memory for the per-frame intermediates (~3.2 KB per frame-row)
+    size_t kmax = opt_.max_span_chunks ? opt_.max_span_chunks : std::max<size_t>(1, 32768 / (size_t)SC_);
+    Kmax_ = (int)std::min<size_t>(kmax, 16384);
+
+    if (!cfg.skip_processing && !opt_.stft_only && !opt_.forced_gains) {
+        if (!weights) throw Error(FVAD_ERR_MODEL, "no NSNet2 weights given");
+        switch (opt_.nn_mode) {
+            case FVAD_NN_F32: nn_ = make_nn_f32(*weights); break;
+            case FVAD_NN_TC_F16X3: nn_ = make_nn_tc(*weights, true); break;
+            case FVAD_NN_TC_F16: nn_ = make_nn_tc(*weights, false); break;
+            default: throw Error(FVAD_ERR_INVALID_ARGUMENT, "unknown nn_mode");
+        }
+    }
+    if (opt_.forced_gains) {
+        const size_t n = (size_t)SC_ * opt_.forced_gain_frames * kBins;
+        forced_.ensure(n);
+        FVAD_CUDA_CHECK(cudaMemcpy(forced_.p, opt_.forced_gains, n * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    for (int i = 0; i < 2; ++i) {
+        halo_[i].ensure((size_t)SC_ * kHop); halo_[i].zero(stream_);
+        tail_[i].ensure((size_t)SC_ * kHop); tail_[i].zero(stream_);
+    }
+    ctx_carry_.ensure((size_t)SC_ * kCtx * kBins); ctx_carry_.zero(stream_);  // NSNet2.zig:79 context rows start at 0.0
+    ylook_carry_.ensure((size_t)SC_ * kYLook); ylook_carry_.zero(stream_);
+    sumsq_carry_.ensure((size_t)SC_); sumsq_carry_.zero(stream_);
+    pend_.ensure((size_t)SC_ * chunk_);
+    d_xptr_.ensure((size_t)SC_);
+    init_machines(cfg);
+    FVAD_CUDA_CHECK(cudaStreamSynchronize(stream_));
+}
+
+Batch::~Batch() {
+    if (stream_) cudaStreamSynchronize(stream_);
+    tables_.release();
+    for (auto &e : ev_) if (e) cudaEventDestroy(e);
+    if (stream_) cudaStreamDestroy(stream_);
+}
+
+
+// One pass over K whole chunks of every stream-channel.  d_x: device array of SC pointers; the
+// span starts x_offset samples into each.
+void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
+    const size_t rows = (size_t)kFrames * K;        // frame rows per stream-channel
+    const size_t frow = (size_t)kCtx + rows;
+    const size_t ypitch = (size_t)kYLook + (size_t)kChunk16 * K;
+    const bool full = !opt_.stft_only;
+    spec_.ensure((size_t)SC_ * rows * kBins);
+    feat_.ensure((size_t)SC_ * frow * kBins);
+    sumsq_.ensure((size_t)SC_ * (K + 1));
+    if (full) {
+        gains_.ensure((size_t)SC_ * rows * kBins);
+        y16_.ensure((size_t)SC_ * ypitch);
+    }
+    cudaStream_t s = stream_;
+
+    // ---- K1 ----
+    FVAD_CUDA_CHECK(cudaEventRecord(ev_[0], s));
+    StftArgs sa;
+    sa.x = d_x; sa.x_offset = x_offset;
+    sa.halo_in = halo_[parity_].p; sa.halo_out = halo_[parity_ ^ 1].p;
+    sa.spec = spec_.p; sa.feat = feat_.p; sa.sumsq = sumsq_.p;
+    sa.K = K; sa.SC = SC_; sa.D = D_;
+    launch_stft(sa, tables_, s);
+    // 4 context feature rows carried from the previous span (NSNet2.zig:188-203)
+    launch_copy_rows(feat_.p, ctx_carry_.p, frow * kBins, (size_t)kCtx * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
+    FVAD_CUDA_CHECK(cudaEventRecord(ev_[1], s));
+
+    const uint64_t span_start = processed_;
+    const uint64_t span_end = processed_ + (uint64_t)K * chunk_;
+    int n_frames = 0;
+    if (full) {
+        // ---- NSNet2 ----
+        if (forced_.p) {
+            const size_t f0 = (size_t)(processed_ / (uint64_t)chunk_) * kFrames;
+            if (f0 + rows > opt_.forced_gain_frames) throw Error(FVAD_ERR_INVALID_ARGUMENT, "forced_gains shorter than the audio");
+            launch_copy_rows(gains_.p, forced_.p + f0 * kBins, rows * kBins, opt_.forced_gain_frames * kBins, rows * kBins, (size_t)SC_, s);
+        } else {
+            NnSpan ns{feat_.p, gains_.p, SC_, K};
+            nn_->forward(ns, s);
+        }
+        FVAD_CUDA_CHECK(cudaEventRecord(ev_[2], s));
+
+        // ---- K3a ----
+        IstftArgs ia;
+        ia.spec = spec_.p; ia.gains = gains_.p;
+        ia.tail_in = tail_[parity_].p; ia.tail_out = tail_[parity_ ^ 1].p;
+        ia.y16 = y16_.p; ia.K = K; ia.SC = SC_;
+        launch_istft(ia, tables_, s);
+        launch_copy_rows(y16_.p, ylook_carry_.p, ypitch, kYLook, kYLook, (size_t)SC_, s);
+        launch_copy_rows(sumsq_.p, sumsq_carry_.p, (size_t)K + 1, 1, 1, (size_t)SC_, s);
+        FVAD_CUDA_CHECK(cudaEventRecord(ev_[3], s));
+
+        // ---- K3b ----
+        const uint64_t frames_end = span_end / (uint64_t)fft_size_;
+        n_frames = (int)(frames_end - frames_done_);
+        if (n_frames > 0) {
+            if (n_frames > max_frames_) {
+                max_frames_ = n_frames + 64;
+                band_.ensure((size_t)n_bands_ * S_ * max_frames_);
+                ratio_.ensure((size_t)S_ * max_frames_);
+                met_.ensure((size_t)S_ * max_frames_);
+            }
+            VadFftArgs va;
+            va.y16 = y16_.p; va.sumsq = sumsq_.p; va.band = band_.p; va.ratio = ratio_.p;
+            va.band_lo = band_lo_.p; va.band_hi = band_hi_.p; va.n_bands = n_bands_;
+            va.S = S_; va.C = C_; va.K = K; va.D = D_;
+            va.span_start = (long long)span_start; va.first_frame = (long long)frames_done_;
+            va.n_frames = n_frames; va.max_frames = max_frames_; va.fft_size = fft_size_; va.chunk = chunk_;
+            va.has_prev_chunk = span_start > 0;
+            launch_vadfft(va, tables_, s);
+        }
+        FVAD_CUDA_CHECK(cudaEventRecord(ev_[4], s));
+
+        // ---- K4 ----
+        if (n_frames > 0) {
+            ScanArgs ca;
+            ca.band = band_.p; ca.ratio = ratio_.p; ca.machines = d_machines_.p; ca.states = d_states_.p;
+            ca.rings = rings_.p; ca.ring_pitch = ring_pitch_; ca.segments = d_segments_.p; ca.max_segments = max_segments_;
+            ca.met = met_.p; ca.S = S_; ca.M = M_; ca.n_frames = n_frames; ca.max_frames = max_frames_;
+            ca.first_frame = (long long)frames_done_; ca.fft_size = fft_size_;
+            launch_vadscan(ca, s);
+        }
+        FVAD_CUDA_CHECK(cudaEventRecord(ev_[5], s));
+    }
+
+    // ---- taps ----
+    if (opt_.keep_taps && taps_.fill_chunks + K <= taps_.cap_chunks) {
+        const size_t trows = (size_t)kFrames * taps_.cap_chunks, off = (size_t)kFrames * taps_.fill_chunks;
+        launch_copy_rows(reinterpret_cast<float *>(taps_.spec.p) + off * kBins * 2, reinterpret_cast<const float *>(spec_.p),
+                         trows * kBins * 2, rows * kBins * 2, rows * kBins * 2, (size_t)SC_, s);
+        launch_copy_rows(taps_.feat.p + off * kBins, feat_.p + (size_t)kCtx * kBins, trows * kBins, frow * kBins, rows * kBins, (size_t)SC_, s);
+        if (full) {
+            launch_copy_rows(taps_.gains.p + off * kBins, gains_.p, trows * kBins, rows * kBins, rows * kBins, (size_t)SC_, s);
+            launch_copy_rows(taps_.y16.p + (size_t)kChunk16 * taps_.fill_chunks, y16_.p + kYLook, (size_t)kChunk16 * taps_.cap_chunks,
+                             ypitch, (size_t)kChunk16 * K, (size_t)SC_, s);
+            // denoised PCM at the input rate (what AudioPipeline.pushDenoisedSamples receives, AudioPipeline.zig:145-167)
+            launch_upsample(y16_.p + kYLook, ypitch, taps_.den.p + (size_t)chunk_ * taps_.fill_chunks, (size_t)chunk_ * taps_.cap_chunks,
+                            (size_t)kChunk16 * K, D_, SC_, s);
+            if (n_frames > 0 && taps_.fill_vad + n_frames <= taps_.cap_vad) {
+                launch_copy_rows(taps_.band.p + taps_.fill_vad, band_.p, taps_.cap_vad, max_frames_, (size_t)n_frames, (size_t)S_, s);
+                launch_copy_rows(taps_.ratio.p + taps_.fill_vad, ratio_.p, taps_.cap_vad, max_frames_, (size_t)n_frames, (size_t)S_, s);
+                FVAD_CUDA_CHECK(cudaMemcpy2DAsync(taps_.met.p + taps_.fill_vad, taps_.cap_vad, met_.p, (size_t)max_frames_,
+                                                  (size_t)n_frames, (size_t)S_, cudaMemcpyDeviceToDevice, s));
+                taps_.fill_vad += n_frames;
+            }
+        }
+        taps_.fill_chunks += K;
+    }
+
+    // ---- carries for the next span ----
+    launch_copy_rows(ctx_carry_.p, feat_.p + rows * kBins, (size_t)kCtx * kBins, frow * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
+    if (full) {
+        launch_copy_rows(ylook_carry_.p, y16_.p + ypitch - kYLook, kYLook, ypitch, kYLook, (size_t)SC_, s);
+        launch_copy_rows(sumsq_carry_.p, sumsq_.p + K, 1, (size_t)K + 1, 1, (size_t)SC_, s);
+    }
+    parity_ ^= 1;
+    processed_ = span_end;
+    frames_done_ += (uint64_t)n_frames;
+    chunks_processed_ += (uint64_t)K * SC_;
+}
+
+
+void Batch::push(const float *const *pcm, size_t n_pointers, size_t n, int memory) {
+    if (n_pointers != (size_t)SC_) throw Error(FVAD_ERR_CHANNEL_COUNT_MISMATCH, "expected n_streams*n_channels planar pointers");
+    if (!pcm) throw Error(FVAD_ERR_INVALID_ARGUMENT, "pcm is NULL");
+    for (int i = 0; i < SC_; ++i) {
+        if (!pcm[i] && n) throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL channel pointer");
+        if (memory == 1 && (reinterpret_cast<uintptr_t>(pcm[i]) & 15)) throw Error(FVAD_ERR_INVALID_ARGUMENT, "device PCM pointers must be 16-byte aligned");
+    }
+    FVAD_CUDA_CHECK(cudaSetDevice(opt_.device));
+    total_written_ += n;
+    if (skip_ || n == 0) return;  // AudioPipeline.maybeRunPipeline: skip_processing (AudioPipeline.zig:211-214)
+
+    cudaStream_t s = stream_;
+    const cudaMemcpyKind kind = memory == 1 ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const size_t total = (size_t)n_pend_ + n;
+    const size_t Ktot = total / (size_t)chunk_;
+    const size_t left = total % (size_t)chunk_;
+
+    // taps cover exactly this push
+    if (opt_.keep_taps) {
+        taps_.fill_chunks = taps_.fill_vad = 0;
+        taps_.cap_chunks = Ktot;
+        taps_.cap_vad = (size_t)((processed_ + Ktot * chunk_) / (uint64_t)fft_size_ - frames_done_);
+        const size_t r = (size_t)SC_ * kFrames * Ktot * kBins;
+        taps_.spec.ensure(std::max<size_t>(r, 1)); taps_.feat.ensure(std::max<size_t>(r, 1)); taps_.gains.ensure(std::max<size_t>(r, 1));
+        taps_.y16.ensure(std::max<size_t>((size_t)SC_ * kChunk16 * Ktot, 1));
+        taps_.den.ensure(std::max<size_t>((size_t)SC_ * chunk_ * Ktot, 1));
+        taps_.band.ensure(std::max<size_t>((size_t)S_ * taps_.cap_vad, 1));
+        taps_.ratio.ensure(std::max<size_t>((size_t)S_ * taps_.cap_vad, 1));
+        taps_.met.ensure(std::max<size_t>((size_t)S_ * taps_.cap_vad, 1));
+    }
+
+    FVAD_CUDA_CHECK(cudaEventRecord(ev_[6], s));
+    if (Ktot > 0) {
+        const bool zero_copy = (memory == 1 && n_pend_ == 0);
+        std::vector<const float *> hx((size_t)SC_);
+        if (zero_copy) {
+            for (int i = 0; i < SC_; ++i) hx[(size_t)i] = pcm[i];
+            FVAD_CUDA_CHECK(cudaMemcpyAsync(d_xptr_.p, hx.data(), hx.size() * sizeof(float *), cudaMemcpyHostToDevice, s));
+            FVAD_CUDA_CHECK(cudaStreamSynchronize(s));  // hx is a stack-lifetime pageable buffer
+            for (size_t k0 = 0; k0 < Ktot; k0 += (size_t)Kmax_) {
+                const int K = (int)std::min<size_t>((size_t)Kmax_, Ktot - k0);
+                process_span(d_xptr_.p, k0 * (size_t)chunk_, K);
+            }
+        } else {
+            // staged: [pending | new samples] per stream-channel, one span at a time
+            const size_t Kst = std::min<size_t>((size_t)Kmax_, Ktot);
+            const size_t spitch = Kst * (size_t)chunk_;
+            stage_.ensure((size_t)SC_ * spitch);
+            for (int i = 0; i < SC_; ++i) hx[(size_t)i] = stage_.p + (size_t)i * spitch;
+            FVAD_CUDA_CHECK(cudaMemcpyAsync(d_xptr_.p, hx.data(), hx.size() * sizeof(float *), cudaMemcpyHostToDevice, s));
+            FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
+            size_t src_off = 0;  // samples of the caller's buffers already consumed
+            for (size_t k0 = 0; k0 < Ktot; k0 += Kst) {
+                const size_t K = std::min<size_t>(Kst, Ktot - k0);
+                const size_t need = K * (size_t)chunk_;
+                const size_t from_pend = (k0 == 0) ? (size_t)n_pend_ : 0;
+                for (int i = 0; i < SC_; ++i) {
+                    float *dst = stage_.p + (size_t)i * spitch;
+                    if (from_pend)
+                        FVAD_CUDA_CHECK(cudaMemcpyAsync(dst, pend_.p + (size_t)i * chunk_, from_pend * sizeof(float), cudaMemcpyDeviceToDevice, s));
+                    FVAD_CUDA_CHECK(cudaMemcpyAsync(dst + from_pend, pcm[i] + src_off, (need - from_pend) * sizeof(float), kind, s));
+                }
+                src_off += need - from_pend;
+                process_span(d_xptr_.p, 0, (int)K);
+            }
+            // the remaining `left` samples start at src_off
+            for (int i = 0; i < SC_ && left; ++i)
+                FVAD_CUDA_CHECK(cudaMemcpyAsync(pend_.p + (size_t)i * chunk_, pcm[i] + src_off, left * sizeof(float), kind, s));
+            n_pend_ = (int)left;
+            goto done;
+        }
+        // zero-copy path: keep the tail that does not fill a chunk
+        for (int i = 0; i < SC_ && left; ++i)
+            FVAD_CUDA_CHECK(cudaMemcpyAsync(pend_.p + (size_t)i * chunk_, pcm[i] + Ktot * (size_t)chunk_, left * sizeof(float), kind, s));
+        n_pend_ = (int)left;
+    } else {
+        for (int i = 0; i < SC_; ++i)
+            FVAD_CUDA_CHECK(cudaMemcpyAsync(pend_.p + (size_t)i * chunk_ + n_pend_, pcm[i], n * sizeof(float), kind, s));
+        n_pend_ = (int)total;
+    }
+done:
+    if (Ktot > 0 && !opt_.stft_only) fetch_segments();
+    FVAD_CUDA_CHECK(cudaEventRecord(ev_[7], s));
+    FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ev_[6], ev_[7]);
+    last_ms_[0] = ms;
+    if (Ktot > 0) {
+        const int last = opt_.stft_only ? 1 : 5;
+        for (int i = 0; i < last; ++i) {
+            cudaEventElapsedTime(&ms, ev_[i], ev_[i + 1]);
+            last_ms_[1 + i] = ms;
+        }
+    }
+    if (segment_overflow_) throw Error(FVAD_ERR_OUT_OF_MEMORY, "segment buffer overflow (more segments than max_segments)");
+}
+
+void Batch::fetch_segments() {
+    const size_t SM = (size_t)S_ * M_;
+    FVAD_CUDA_CHECK(cudaMemcpyAsync(h_states_.data(), d_states_.p, SM * sizeof(ScanState), cudaMemcpyDeviceToHost, stream_));
+    FVAD_CUDA_CHECK(cudaStreamSynchronize(stream_));
+    // copy only the new segments of each (stream, machine)
+    if (seg_seen_.size() != SM) seg_seen_.assign(SM, 0);
+    for (size_t t = 0; t < SM; ++t) {
+        unsigned have = h_states_[t].n_segments;
+        if (have > (unsigned)max_segments_) { segment_overflow_ = true; have = (unsigned)max_segments_; }
+        if (have > seg_seen_[t]) {
+            FVAD_CUDA_CHECK(cudaMemcpyAsync(h_segments_.data() + t * max_segments_ + seg_seen_[t],
+                                            d_segments_.p + t * max_segments_ + seg_seen_[t],
+                                            (have - seg_seen_[t]) * sizeof(fvad_segment), cudaMemcpyDeviceToHost, stream_));
+            seg_seen_[t] = have;
+        }
+    }
+}
+
+void Batch::segments(size_t stream, size_t machine, const fvad_segment **segs, size_t *n) {
+    if (stream >= (size_t)S_ || machine >= (size_t)M_) throw Error(FVAD_ERR_INVALID_ARGUMENT, "stream/machine index out of range");
+    const size_t t = stream * M_ + machine;
+    if (segs) *segs = h_segments_.data() + t * max_segments_;
+    if (n) *n = seg_seen_.empty() ? 0 : seg_seen_[t];
+}
+
+size_t Batch::tap(int which, void *dst, size_t dst_bytes) {
+    const size_t rows = (size_t)SC_ * kFrames * taps_.fill_chunks * kBins;
+    const void *src = nullptr;
+    size_t elems = 0, esz = 4;
+    switch (which) {
+        case FVAD_TAP_SPECTRUM: src = taps_.spec.p; elems = rows; esz = sizeof(fvad_complex); break;
+        case FVAD_TAP_FEATURES: src = taps_.feat.p; elems = rows; break;
+        case FVAD_TAP_GAINS: src = taps_.gains.p; elems = rows; break;
+        case FVAD_TAP_DENOISED16: src = taps_.y16.p; elems = (size_t)SC_ * kChunk16 * taps_.fill_chunks; break;
+        case FVAD_TAP_DENOISED: src = taps_.den.p; elems = (size_t)SC_ * chunk_ * taps_.fill_chunks; break;
+        case FVAD_TAP_BAND: src = taps_.band.p; elems = (size_t)S_ * taps_.fill_vad; break;
+        case FVAD_TAP_RATIO: src = taps_.ratio.p; elems = (size_t)S_ * taps_.fill_vad; break;
+        case FVAD_TAP_MET: src = taps_.met.p; elems = (size_t)S_ * taps_.fill_vad; esz = 1; break;
+        default: throw Error(FVAD_ERR_INVALID_ARGUMENT, "unknown tap");
+    }
+    if (!opt_.keep_taps) throw Error(FVAD_ERR_INVALID_ARGUMENT, "taps were not enabled (fvad_batch_options.keep_taps)");
+    if (dst) {
+        if (dst_bytes < elems * esz) throw Error(FVAD_ERR_INVALID_RESULT_LENGTH, "tap destination too small");
+        if (elems) FVAD_CUDA_CHECK(cudaMemcpy(dst, src, elems * esz, cudaMemcpyDeviceToHost));
+    }
+    return elems;
+}
+
+void Batch::stats(fvad_batch_stats *out) const {
+    memset(out, 0, sizeof(*out));
+    out->kernel_launches = g_kernel_launches - launches0_;
+    out->chunks_processed = chunks_processed_;
+    out->vad_frames = frames_done_;
+    out->last_push_device_ms = last_ms_[0];
+    out->last_stft_ms = last_ms_[1]; out->last_nn_ms = last_ms_[2]; out->last_istft_ms = last_ms_[3];
+    out->last_vadfft_ms = last_ms_[4]; out->last_scan_ms = last_ms_[5];
+}
+
+}  // namespace fvad

@@ -1,0 +1,99 @@
+// engine.cuh -- the batch engine: S independent pipelines (streams) x C channels advanced in lock
+// step on one GPU.  Host-side restatement of the step order of the reference's
+// AudioPipeline.pushSamples (src/AudioPipeline.zig:118-143) -> VADPipeline.collectInputStep /
+// denoiserStep / fftStep / stateMachineStep (src/AudioPipeline/VADPipeline.zig:140-237), with time
+// folded into the batch: every complete chunk of every stream-channel is processed in one pass
+// K1 (stft) -> NN -> K3a (istft) -> K3b (vadfft) -> K4 (vadscan); the only state carried between
+// passes is the halo set of SURVEY App. B (160 input samples, 4 feature rows, 160 output samples,
+// 1024 denoised samples, one chunk ratio, the VAD machine states).
+#pragma once
+#include <memory>
+#include <vector>
+
+#include "kernels.cuh"
+#include "nn.cuh"
+
+namespace fvad {
+
+struct MachineDerived {
+    ScanMachine dev;
+    int bin_lo, bin_hi;
+};
+
+class Batch {
+public:
+    Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weights, const fvad_batch_options &opt);
+    ~Batch();
+
+    // pcm: S*C planar pointers (stream-major), n samples each; memory 0 host / 1 device
+    void push(const float *const *pcm, size_t n_pointers, size_t n_samples, int memory);
+    void segments(size_t stream, size_t machine, const fvad_segment **segs, size_t *n);
+    size_t tap(int which, void *dst, size_t dst_bytes);
+    void stats(fvad_batch_stats *out) const;
+    uint64_t total_write_count() const { return total_written_; }
+    size_t n_machines() const { return (size_t)M_; }
+    size_t n_streams() const { return (size_t)S_; }
+    size_t n_channels() const { return (size_t)C_; }
+    size_t chunk() const { return (size_t)chunk_; }
+
+private:
+    void process_span(const float *const *d_x, size_t x_offset, int K);
+    void init_machines(const fvad_config &cfg);
+    void fetch_segments();
+
+    int S_, C_, SC_, D_, chunk_, M_, fft_size_;
+    size_t sample_rate_;
+    fvad_batch_options opt_;
+    int Kmax_;
+    cudaStream_t stream_ = nullptr;
+    cudaEvent_t ev_[8] = {};
+    Tables tables_;
+    std::unique_ptr<NnBackend> nn_;
+    std::vector<MachineDerived> machines_;
+    int n_bands_ = 0;
+
+    // progress
+    uint64_t total_written_ = 0;   // samples pushed per channel
+    uint64_t processed_ = 0;       // samples consumed in whole chunks (per channel)
+    uint64_t frames_done_ = 0;     // VAD frames produced per stream
+    int n_pend_ = 0;               // samples waiting in pend_ (per channel)
+    int parity_ = 0;               // which halo/tail carry buffer is current
+
+    // device state
+    DevBuf<float> pend_, stage_;               // [SC][chunk], [SC][Kstage*chunk]
+    DevBuf<const float *> d_xptr_;             // [SC]
+    DevBuf<float> halo_[2], tail_[2];          // [SC][160]
+    DevBuf<float> ctx_carry_, ylook_carry_, sumsq_carry_;
+    DevBuf<fvad_complex> spec_;
+    DevBuf<float> feat_, gains_, y16_, sumsq_, band_, ratio_;
+    DevBuf<unsigned char> met_;
+    DevBuf<int> band_lo_, band_hi_;
+    DevBuf<ScanMachine> d_machines_;
+    DevBuf<ScanState> d_states_;
+    DevBuf<double> rings_;
+    DevBuf<fvad_segment> d_segments_;
+    DevBuf<float> forced_;
+    int ring_pitch_ = 0, max_segments_ = 0, max_frames_ = 0;
+
+    // host results
+    std::vector<ScanState> h_states_;
+    std::vector<fvad_segment> h_segments_;
+    std::vector<unsigned> seg_seen_;
+    bool segment_overflow_ = false;
+    bool skip_ = false;
+
+    // taps of the last push
+    struct Taps {
+        size_t frames = 0, chunks = 0, vad_frames = 0;  // per stream-channel / per stream
+        DevBuf<fvad_complex> spec;
+        DevBuf<float> feat, gains, y16, den, band, ratio;
+        DevBuf<unsigned char> met;
+        size_t fill_chunks = 0, fill_vad = 0, cap_chunks = 0, cap_vad = 0;
+    } taps_;
+
+    // stats
+    uint64_t launches0_ = 0, chunks_processed_ = 0;
+    double last_ms_[6] = {};
+};
+
+}  // namespace fvad

@@ -1,0 +1,152 @@
+// fft_dev.cuh -- warp-level complex FFT of length N = 32*R, all butterflies in registers and
+// warp shuffles (no shared-memory passes inside the transform).
+//
+// Replaces kissfft's mixed-radix kf_work (reference lib/kissfft/kiss_fft.c:236-300) for the two
+// transform sizes on the hot path: real 320 -> complex 160 (R=5) and real 1024 -> complex 512
+// (R=16).  Different algorithm, same mathematics: a Cooley-Tukey split N = R x 32 where
+//   * lane l holds v[a] = z[l + 32a], a in [0,R)            (coalesced float2 loads)
+//   * a length-R DFT runs over a inside each lane            (registers)
+//   * twiddle w_N^(l*k1)
+//   * a length-32 DFT runs across the lanes for every k1     (5 shuffle-xor DIF stages)
+// Result: lane l, register k1 holds Z[k1 + R*bitrev5(l)].
+//
+// Twiddles come from a shared-memory table T[j] = exp(-2*pi*i*j/(2N)), j in [0,2N), computed on
+// the host in double and rounded to float (same recipe as kiss_fft.c:361-367).
+#pragma once
+
+#include <cuda_runtime.h>
+
+namespace fvad {
+
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+template <bool INV>
+__device__ __forceinline__ float2 tw(float2 w) { return INV ? make_float2(w.x, -w.y) : w; }
+__device__ __forceinline__ int bitrev5(int l) { return (int)(__brev((unsigned)l) >> 27); }
+
+// ---- in-register DFT of length R (forward: e^{-i...}; INV: e^{+i...}), unnormalised ----
+template <int R, bool INV>
+struct RegDft;
+
+template <bool INV>
+struct RegDft<1, INV> {
+    static __device__ __forceinline__ void run(float2 (&)[1]) {}
+};
+
+// power-of-two R by recursive decimation in time; twiddles are literal constants so the
+// trivial ones fold away at compile time.
+template <int R, int K>
+__device__ __forceinline__ float2 w_const() {
+    // exp(-2*pi*i*K/R) for R in {2,4,8,16}
+    constexpr float c16[16] = {1.0f, 0.92387953251128674f, 0.70710678118654752f, 0.38268343236508977f,
+                               0.0f, -0.38268343236508977f, -0.70710678118654752f, -0.92387953251128674f,
+                               -1.0f, -0.92387953251128674f, -0.70710678118654752f, -0.38268343236508977f,
+                               0.0f, 0.38268343236508977f, 0.70710678118654752f, 0.92387953251128674f};
+    constexpr int j = (K * (16 / R)) & 15;
+    // sin(2*pi*j/16) = cos(2*pi*(j-4)/16)
+    return make_float2(c16[j], -c16[(j + 12) & 15]);
+}
+
+template <int R, bool INV>
+struct RegDft {
+    static_assert(R == 2 || R == 4 || R == 8 || R == 16, "power-of-two register DFT");
+    template <int K>
+    static __device__ __forceinline__ void bfly(float2 (&v)[R], const float2 (&e)[R / 2], const float2 (&o)[R / 2]) {
+        if constexpr (K < R / 2) {
+            const float2 t = cmul(o[K], tw<INV>(w_const<R, K>()));
+            v[K] = cadd(e[K], t);
+            v[K + R / 2] = csub(e[K], t);
+            bfly<K + 1>(v, e, o);
+        }
+    }
+    static __device__ __forceinline__ void run(float2 (&v)[R]) {
+        float2 e[R / 2], o[R / 2];
+#pragma unroll
+        for (int i = 0; i < R / 2; ++i) {
+            e[i] = v[2 * i];
+            o[i] = v[2 * i + 1];
+        }
+        RegDft<R / 2, INV>::run(e);
+        RegDft<R / 2, INV>::run(o);
+        bfly<0>(v, e, o);
+    }
+};
+
+template <bool INV>
+struct RegDft<5, INV> {
+    static __device__ __forceinline__ void run(float2 (&v)[5]) {
+        constexpr float c1 = 0.30901699437494742f, c2 = -0.80901699437494742f;  // cos(2pi/5), cos(4pi/5)
+        constexpr float s1 = 0.95105651629515357f, s2 = 0.58778525229247313f;   // sin(2pi/5), sin(4pi/5)
+        const float2 a1 = cadd(v[1], v[4]), d1 = csub(v[1], v[4]);
+        const float2 a2 = cadd(v[2], v[3]), d2 = csub(v[2], v[3]);
+        const float2 A = make_float2(v[0].x + c1 * a1.x + c2 * a2.x, v[0].y + c1 * a1.y + c2 * a2.y);
+        const float2 B = make_float2(v[0].x + c2 * a1.x + c1 * a2.x, v[0].y + c2 * a1.y + c1 * a2.y);
+        // P = s1*d1 + s2*d2 ; Q = s2*d1 - s1*d2 ; forward: Y1 = A - iP, Y4 = A + iP, Y2 = B - iQ, Y3 = B + iQ
+        const float2 P = make_float2(s1 * d1.x + s2 * d2.x, s1 * d1.y + s2 * d2.y);
+        const float2 Q = make_float2(s2 * d1.x - s1 * d2.x, s2 * d1.y - s1 * d2.y);
+        // -i*(x+iy) = (y, -x)
+        const float2 mP = INV ? make_float2(-P.y, P.x) : make_float2(P.y, -P.x);
+        const float2 mQ = INV ? make_float2(-Q.y, Q.x) : make_float2(Q.y, -Q.x);
+        v[0] = make_float2(v[0].x + a1.x + a2.x, v[0].y + a1.y + a2.y);
+        v[1] = cadd(A, mP);
+        v[4] = csub(A, mP);
+        v[2] = cadd(B, mQ);
+        v[3] = csub(B, mQ);
+    }
+};
+
+// Complex FFT over one warp.  T: shared-memory table of 2N entries (see header comment).
+template <int R, bool INV>
+__device__ __forceinline__ void warp_cfft(float2 (&v)[R], const float2 *__restrict__ T, int lane) {
+    constexpr int N = 32 * R;
+    RegDft<R, INV>::run(v);
+#pragma unroll
+    for (int k1 = 1; k1 < R; ++k1) v[k1] = cmul(v[k1], tw<INV>(T[2 * lane * k1]));
+#pragma unroll
+    for (int h = 16; h >= 1; h >>= 1) {
+        const bool upper = (lane & h) != 0;
+        const float2 w = tw<INV>(T[(lane & (h - 1)) * (N / h)]);
+#pragma unroll
+        for (int k1 = 0; k1 < R; ++k1) {
+            float2 b;
+            b.x = __shfl_xor_sync(0xffffffffu, v[k1].x, h);
+            b.y = __shfl_xor_sync(0xffffffffu, v[k1].y, h);
+            v[k1] = upper ? cmul(csub(b, v[k1]), w) : cadd(v[k1], b);
+        }
+    }
+}
+
+// index of the value held by (lane, register k1) after warp_cfft
+template <int R>
+__device__ __forceinline__ int cfft_out_index(int lane, int k1) { return k1 + R * bitrev5(lane); }
+
+// Real-FFT unpack (what kiss_fftr.c:93-116 does): bin k of the length-2N real transform from the
+// complex transform Z of the packed signal.  k in [0,N]; Z indices are taken mod N.
+__device__ __forceinline__ float2 rfft_bin(const float2 *__restrict__ Z, const float2 *__restrict__ T, int N, int k) {
+    const float2 a = Z[k == N ? 0 : k];
+    const float2 bb = Z[k == 0 ? 0 : N - k];
+    const float2 b = make_float2(bb.x, -bb.y);
+    const float2 e = cadd(a, b), d = csub(a, b);
+    // o = d * (-i * T[k])   (kissfft's super twiddle exp(-i*pi*(k/N + 1/2)))
+    const float2 t = T[k];
+    const float2 mi_t = make_float2(t.y, -t.x);  // -i*(x+iy) = (y,-x)
+    const float2 o = cmul(d, mi_t);
+    // DC and Nyquist are purely real (kiss_fftr.c:82-89 writes their imaginary part as 0)
+    return make_float2((e.x + o.x) * 0.5f, (k == 0 || k == N) ? 0.0f : (e.y + o.y) * 0.5f);
+}
+
+// Inverse pre-pack (kiss_fftri, kiss_fftr.c:131-153): Zt[k] = (X[k]+conj(X[N-k])) + i*conj(T[k])*(X[k]-conj(X[N-k]))
+__device__ __forceinline__ float2 irfft_pack(const float2 *__restrict__ X, const float2 *__restrict__ T, int N, int k) {
+    const float2 a = X[k];
+    const float2 bb = X[N - k];
+    const float2 b = make_float2(bb.x, -bb.y);
+    const float2 e = cadd(a, b), d = csub(a, b);
+    const float2 t = T[k];                       // (c, s) = exp(-i*pi*k/N)  -> conj = (c, -s)
+    const float2 it = make_float2(t.y, t.x);     // i*(c - i s) = (s, c)
+    return cadd(e, cmul(d, it));
+}
+
+}  // namespace fvad

@@ -1,0 +1,163 @@
+// vadfft.cu -- K3b: 1:D linear upsample of the denoised stream, re-blocking into non-overlapping
+// 1024-sample frames, periodic-Hann real FFT-1024, magnitude * 1/sum(w), speech-band sum, min over
+// channels; plus the sample-weighted raw inter-channel volume ratio of the frame.
+//
+// Replaces (reference):
+//   resample.upsampleAudio / interpolate  (audio_utils/resample.zig:32-79; lerp is a fused a+(b-a)*t)
+//   BufferedFFT.write re-blocking         (AudioPipeline/BufferedFFT.zig:129-160, SegmentWriter.zig:46-109)
+//   BufferedFFT.fft                       (BufferedFFT.zig:162-181) -> FFT.fft -> kiss_fftr 1024
+//   BufferedFFT.averageVolumeInBand       (BufferedFFT.zig:183-202)  sequential f32 sum of bins lo..hi
+//   min over channels                     (AudioPipeline/VADMachine.zig:153-158, start value 999)
+//   BufferedVolumeAnalyzer.analyseVolume  (BufferedVolumeAnalyzer.zig:48-69) from the chunk sums of squares
+//   VADMetadata weighted merge            (VADMetadata.zig:29-60) through the three buffered steps
+//
+// One CTA per (VAD frame, stream); warp w handles channel w (channels beyond the warp count loop).
+#include "fft_dev.cuh"
+#include "kernels.cuh"
+
+namespace fvad {
+
+constexpr int kVadWarps = 2;
+constexpr int kVadThreads = 32 * kVadWarps;
+constexpr int kMaxBands = 8;
+
+// ratio of one chunk as the reference sees it after the analyser and the denoiser step have each
+// pushed it with weight `chunk` and divided it out again (f32, no contraction)
+__device__ __forceinline__ float chunk_ratio(const float *__restrict__ sumsq, int C, int s, int pitch, int slot, int chunk) {
+    float vmin = 1.0f, vmax = 0.0f;
+    for (int ch = 0; ch < C; ++ch) {
+        const float ss = sumsq[(size_t)(s * C + ch) * pitch + slot];
+        const float v = sqrtf(__fdiv_rn(ss, (float)chunk));  // audio_utils.zig:22-23
+        if (v < vmin) vmin = v;
+        if (v > vmax) vmax = v;
+    }
+    float r = (vmax == 0.0f) ? 0.0f : __fdiv_rn(vmin, vmax);
+    const float w = (float)chunk;
+    r = __fdiv_rn(__fmul_rn(r, w), w);  // BufferedVolumeAnalyzer.write :35-43
+    r = __fdiv_rn(__fmul_rn(r, w), w);  // BufferedDenoiser.write :83-86,114
+    return r;
+}
+
+template <int D>
+__global__ void __launch_bounds__(kVadThreads) vadfft_kernel(VadFftArgs a, const float2 *__restrict__ gT,
+                                                             const float *__restrict__ ghann, float norm) {
+    __shared__ float2 T[1024];
+    __shared__ float2 zb[kVadWarps][512];
+    __shared__ float chband[kVadWarps][kMaxBands];
+
+    const int fi = blockIdx.x;  // frame within this launch
+    const int s = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 1024; i += kVadThreads) T[i] = gT[i];
+    __syncthreads();
+
+    const long long frame = a.first_frame + fi;
+    const long long s0 = frame * 1024;                 // absolute start sample (input rate)
+    const long long rel = s0 - a.span_start;           // relative to the span start, may be negative
+    const size_t ypitch = kYLook + (size_t)kChunk16 * a.K;
+
+    float bmin[kMaxBands];
+#pragma unroll
+    for (int b = 0; b < kMaxBands; ++b) bmin[b] = 999.0f;
+
+    for (int ch0 = 0; ch0 < a.C; ch0 += kVadWarps) {
+        const int ch = ch0 + warp;
+        if (ch < a.C) {
+            // y16 index 0 of the span sits at +kYLook; (rel + i) is the 48 k (input-rate) offset
+            const float *__restrict__ y = a.y16 + (size_t)(s * a.C + ch) * ypitch + kYLook;
+            float2 v[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const int n = lane + 32 * q;
+                float e[2];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const long long p = rel + 2 * n + j;
+                    float val;
+                    if (D == 1) {
+                        val = y[p];
+                    } else {
+                        // resample.zig:44-59: position 3m+2 carries y16[m]; 3m and 3m+1 interpolate from y16[m-1]
+                        const long long m = (p >= 0) ? p / D : -((-p + D - 1) / D);
+                        const int ph = (int)(p - m * D);
+                        const float cur = y[m];
+                        if (ph == D - 1) val = cur;
+                        else {
+                            const float prev = y[m - 1];
+                            const float frac = __fdiv_rn((float)(ph + 1), (float)D);
+                            val = fmaf(cur - prev, frac, prev);
+                        }
+                    }
+                    e[j] = val;
+                }
+                const float2 w2 = __ldg(reinterpret_cast<const float2 *>(ghann) + n);
+                v[q] = make_float2(e[0] * w2.x, e[1] * w2.y);
+            }
+            warp_cfft<16, false>(v, T, lane);
+#pragma unroll
+            for (int k1 = 0; k1 < 16; ++k1) zb[warp][cfft_out_index<16>(lane, k1)] = v[k1];
+            __syncwarp();
+            // magnitudes of the bins any band needs -> reuse zb's own storage is unsafe; use registers + shuffles:
+            // each band is at most a few dozen bins; lane 0 accumulates sequentially in index order.
+            for (int b = 0; b < a.n_bands; ++b) {
+                const int lo = a.band_lo[b], hi = a.band_hi[b];
+                float acc = 0.0f;
+                for (int base = lo; base <= hi; base += 32) {
+                    const int k = base + lane;
+                    float mag = 0.0f;
+                    if (k <= hi) {
+                        const float2 X = rfft_bin(zb[warp], T, 512, k);
+                        // FFT.zig:16-18 abs = sqrt(r*r + i*i); BufferedFFT.zig:176 * norm_factor
+                        mag = __fmul_rn(sqrtf(__fadd_rn(__fmul_rn(X.x, X.x), __fmul_rn(X.y, X.y))), norm);
+                    }
+                    const int cnt = min(32, hi - base + 1);
+                    for (int j = 0; j < cnt; ++j) acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, mag, j));
+                }
+                if (lane == 0) chband[warp][b] = acc;
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        if (tid == 0) {
+            for (int w = 0; w < kVadWarps && ch0 + w < a.C; ++w)
+                for (int b = 0; b < a.n_bands; ++b) bmin[b] = fminf(bmin[b], chband[w][b]);
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        for (int b = 0; b < a.n_bands; ++b) a.band[((size_t)b * a.S + s) * a.max_frames + fi] = bmin[b];
+        // VADMetadata merge over the (at most two) chunks this frame draws samples from
+        const int pitch = 1 + a.K;
+        const long long e0 = s0 + 1023;
+        const long long c_first = (s0 >= a.span_start) ? (rel / a.chunk) : -1;     // -1 = previous span's last chunk
+        const long long c_last = (e0 - a.span_start) / a.chunk;                    // e0 >= span_start always
+        float sum = 0.0f, wsum = 0.0f;
+        if (c_first == c_last) {
+            const float r = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_first + 1, a.chunk);
+            sum = __fmul_rn(r, 1024.0f);
+            wsum = 1024.0f;
+        } else {
+            const long long boundary = a.span_start + c_last * a.chunk;  // first sample of the later chunk
+            const float n0 = (float)(boundary - s0), n1 = (float)(s0 + 1024 - boundary);
+            const float r0 = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_first + 1, a.chunk);
+            const float r1 = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_last + 1, a.chunk);
+            sum = __fadd_rn(__fmul_rn(r0, n0), __fmul_rn(r1, n1));
+            wsum = __fadd_rn(n0, n1);
+        }
+        a.ratio[(size_t)s * a.max_frames + fi] = __fdiv_rn(sum, wsum);
+    }
+}
+
+void launch_vadfft(const VadFftArgs &a, const Tables &t, cudaStream_t s) {
+    if (a.n_frames <= 0 || a.S <= 0) return;
+    if (a.n_bands > kMaxBands) throw Error(FVAD_ERR_INVALID_ARGUMENT, "too many distinct speech bands");
+    if (a.fft_size != 1024) throw Error(FVAD_ERR_INVALID_FFT_SIZE, "GPU VAD path supports fft_size 1024");
+    dim3 grid((unsigned)a.n_frames, (unsigned)a.S);
+    if (a.D == 1) vadfft_kernel<1><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
+    else if (a.D == 3) vadfft_kernel<3><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
+    else throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "unsupported upsample factor");
+    FVAD_LAUNCHED();
+    FVAD_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace fvad

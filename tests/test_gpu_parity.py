@@ -1,0 +1,227 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the CPU oracle on the
+same seeded inputs.  Tolerances are the north-star's: spectra and gains within 1e-4 relative
+(relative to the frame's largest magnitude for near-zero bins), per-frame VAD decisions
+>= 99.9 %, segment boundaries within +-1 frame."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-4
+
+
+def rel_err_rows(a, b):
+    """max over rows of |a-b| / max|b| per row."""
+    a = np.asarray(a); b = np.asarray(b)
+    d = np.abs(a - b).reshape(a.shape[0], -1).max(axis=1)
+    s = np.abs(b).reshape(b.shape[0], -1).max(axis=1)
+    return float((d / np.maximum(s, 1e-30)).max())
+
+
+@pytest.mark.parametrize("n", [320, 1024, 64, 128, 256, 512])
+def test_fft_operator_matches_oracle(fv, po, n):
+    rng = np.random.default_rng(n)
+    x = rng.standard_normal((37, n)).astype(np.float32)
+    w = rng.uniform(0.1, 1.0, n).astype(np.float32)
+    f = fv.FFT(n, 16000)
+    got = f.fft_batch(x, w)
+    ref = po.rfft(x, w)
+    assert rel_err_rows(got, ref) < 2e-6
+    one = f.fft(x[0][: n // 3], w, x[0][n // 3:])  # SplitSlice form
+    assert rel_err_rows(one[None], ref[:1]) < 2e-6
+    inv = fv.FFT(n, 16000, True)
+    back = inv.inv_fft_batch(ref)
+    refb = po.irfft(ref, n)
+    assert rel_err_rows(back, refb) < 2e-6
+    assert rel_err_rows(inv.inv_fft(ref[0])[None], refb[:1]) < 2e-6
+
+
+def test_fft_operator_errors(fv):
+    with pytest.raises(fv.FvadError) as e:
+        fv.FFT(321, 16000)
+    assert e.value.name == "InvalidFFTSize"
+    f = fv.FFT(320, 16000)
+    w = np.ones(320, np.float32)
+    with pytest.raises(fv.FvadError) as e:
+        f.fft(np.zeros(319, np.float32), w)
+    assert e.value.name == "InvalidSamplesLength"
+    with pytest.raises(fv.FvadError) as e:
+        f.fft(np.zeros(320, np.float32), w[:100])
+    assert e.value.name == "InvalidWindowLength"
+    with pytest.raises(fv.FvadError) as e:
+        f.fft(np.zeros(320, np.float32), w, n_bins=160)
+    assert e.value.name == "InvalidResultLength"
+    with pytest.raises(fv.FvadError) as e:
+        f.inv_fft(np.zeros(160, np.complex64))
+    assert e.value.name == "InvalidBinsLength"
+    assert f.bin_count() == 161 and abs(f.bin_width() - 50.0) < 1e-6
+    assert f.freq_to_bin(500.0) == 10
+    with pytest.raises(fv.FvadError) as e:
+        f.freq_to_bin(9000.0)
+    assert e.value.name == "OutOfRange"
+    with pytest.raises(fv.FvadError) as e:
+        f.freq_to_bin(-1.0)
+    assert e.value.name == "NegativeFrequency"
+    g = fv.FFT(1024, 48000)
+    assert g.freq_to_bin(500.0) == 11 and g.freq_to_bin(2000.0) == 43
+
+
+def _run_both(fv, po, wd, sr, nch, seconds, seed, nn_mode=0, pushes=1, alts=None, forced=False):
+    x, _ = fv.synth.onboard_stream(seed, seconds, 16000, nch)
+    if sr == 48000:
+        x = fv.synth.expand_16k_to_48k(x)
+    o_alts = None
+    if alts:
+        o_alts = [po.VadMachineConfig.default(**a) for a in alts]
+    fg = None
+    if forced:
+        rng = np.random.default_rng(seed + 1)
+        nfr = (x.shape[1] // (8000 * sr // 16000)) * 50
+        fg = rng.uniform(-0.2, 1.2, (nch, nfr, 161)).astype(np.float32)
+    op = po.Pipeline(None if forced else wd, sr, nch, alts=o_alts, keep_denoised=True, keep_nn=True, forced_gains=fg)
+    g_alts = [fv.vad_machine_config(**a) for a in alts] if alts else None
+    gp = fv.BatchPipeline(1, sr, nch, None if forced else wd, alt_vad_machine_configs=g_alts, nn_mode=nn_mode,
+                          keep_taps=True, forced_gains=fg)
+    return x, op, gp
+
+
+@pytest.mark.parametrize("sr,nch", [(16000, 1), (48000, 1), (48000, 2)])
+def test_full_pipeline_parity_single_push(fv, po, wd, sr, nch):
+    x, op, gp = _run_both(fv, po, wd, sr, nch, 31.3, seed=11 + nch)
+    op.push_samples(x)
+    gp.push(x)
+    feat, gain, spec = op.nn_taps()  # channel 0
+    nfr = feat.shape[0]
+    g_spec = gp.tap(fv.capi.TAP_SPECTRUM)[0]
+    g_feat = gp.tap(fv.capi.TAP_FEATURES)[0]
+    g_gain = gp.tap(fv.capi.TAP_GAINS)[0]
+    assert g_spec.shape[0] == nfr
+    assert rel_err_rows(g_spec, spec) < REL
+    # features are log10 of the power: compare where the power is not at the numerical floor of the frame
+    pw = np.abs(spec) ** 2
+    ok = pw > (pw.max(axis=1, keepdims=True) * 1e-9)
+    assert np.abs(g_feat - feat)[ok].max() < 1e-3
+    assert np.abs(g_gain - gain).max() / np.abs(gain).max() < REL
+    for c in range(nch):
+        d_ref = op.denoised(c)
+        d_gpu = gp.tap(fv.capi.TAP_DENOISED)[c]
+        assert d_gpu.shape == d_ref.shape
+        assert np.abs(d_gpu - d_ref).max() < REL * max(np.abs(d_ref).max(), 1e-3)
+    band, ratio, met = op.frames()
+    g_band = gp.tap(fv.capi.TAP_BAND)[0]
+    g_ratio = gp.tap(fv.capi.TAP_RATIO)[0]
+    g_met = gp.tap(fv.capi.TAP_MET)[0]
+    assert g_band.shape == band.shape and len(band) == (x.shape[1] // (8000 * sr // 16000)) * (8000 * sr // 16000) // 1024
+    assert np.abs(g_band - band).max() < 2e-4 * np.abs(band).max()
+    assert np.abs(g_ratio - ratio).max() < 1e-5
+    assert (g_met == met).mean() >= 0.999
+    assert _segments_close(gp.segments(0), op.segments(0), 1024)
+
+
+def _segments_close(a, b, tol):
+    if len(a) != len(b):
+        return False
+    for (f0, t0, r0, m0), (f1, t1, r1, m1) in zip(a, b):
+        if abs(int(f0) - int(f1)) > tol or abs(int(t0) - int(t1)) > tol:
+            return False
+        if abs(r0 - r1) > 1e-3 or abs(m0 - m1) > 1024 / 16000 + 1e-3:
+            return False
+    return True
+
+
+def test_dsp_parity_with_forced_gains_is_tight(fv, po, wd):
+    """With the network taken out (same gains fed to both sides) everything downstream of the STFT
+    must agree to float rounding: isolates DSP parity from NN parity."""
+    x, op, gp = _run_both(fv, po, wd, 48000, 2, 20.0, seed=5, forced=True)
+    op.push_samples(x)
+    gp.push(x)
+    for c in range(2):
+        d_ref, d_gpu = op.denoised(c), gp.tap(fv.capi.TAP_DENOISED)[c]
+        assert np.abs(d_gpu - d_ref).max() < 2e-6 * max(np.abs(d_ref).max(), 1e-3)
+    band, ratio, met = op.frames()
+    assert np.abs(gp.tap(fv.capi.TAP_BAND)[0] - band).max() < 5e-6 * np.abs(band).max()
+    assert np.abs(gp.tap(fv.capi.TAP_RATIO)[0] - ratio).max() < 1e-6
+    assert (gp.tap(fv.capi.TAP_MET)[0] == met).all()
+    assert gp.segments(0) == op.segments(0) or _segments_close(gp.segments(0), op.segments(0), 0)
+
+
+def test_ragged_pushes_equal_one_push(fv, po, wd):
+    """Chunk/halo carries: pushing in ragged pieces (not multiples of the chunk, spans of 2 chunks)
+    gives the same segments and taps as the oracle fed the same way."""
+    sr, nch = 48000, 1
+    x, op, _ = _run_both(fv, po, wd, sr, nch, 40.0, seed=21)
+    gp = fv.BatchPipeline(1, sr, nch, wd, keep_taps=True, max_span_chunks=2)
+    cuts = [0, 1000, 24000 + 17, 100000, 100001, 480000, x.shape[1]]
+    bands = []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        first = op.push_samples(x[:, a:b])
+        assert first == a
+        gp.push(x[:, a:b])
+        t = gp.tap(fv.capi.TAP_BAND)
+        if t.size:
+            bands.append(t[0])
+    band, ratio, met = op.frames()
+    g_band = np.concatenate(bands)
+    assert g_band.shape == band.shape
+    assert np.abs(g_band - band).max() < 2e-4 * np.abs(band).max()
+    assert _segments_close(gp.segments(0), op.segments(0), 1024)
+
+
+def test_alt_machines_and_batch_of_streams(fv, po, wd):
+    """BASELINE config 5 in miniature: several VADMachine configs over several streams."""
+    sr = 16000
+    alts = [dict(speech_threshold_factor=4.0), dict(speech_threshold_factor=16.0, max_speech_gap_sec=1.0),
+            dict(min_consecutive_sec_to_open=0.4, channel_vol_ratio_threshold=0.4)]
+    S = 3
+    xs = [fv.synth.onboard_stream(100 + s, 45.0, sr, 1)[0] for s in range(S)]
+    gp = fv.BatchPipeline(S, sr, 1, wd, alt_vad_machine_configs=[fv.vad_machine_config(**a) for a in alts])
+    gp.push(np.concatenate(xs, axis=0))
+    for s in range(S):
+        op = po.Pipeline(wd, sr, 1, alts=[po.VadMachineConfig.default(**a) for a in alts])
+        op.push_samples(xs[s])
+        for m in range(1 + len(alts)):
+            assert _segments_close(gp.segments(s, m), op.segments(m), 1024), (s, m)
+
+
+def test_nsnet2_operator_and_pipeline_facade(fv, po, wd):
+    sr = 48000
+    x, _ = fv.synth.onboard_stream(3, 2.0, 16000, 1)
+    x = fv.synth.expand_16k_to_48k(x)[0]
+    chunk = fv.NSNet2.get_chunk_size(sr)
+    assert chunk == 24000
+    ns = fv.NSNet2(sr, weights=wd)
+    L = po.lib()
+    ws, keep = po.make_weights_struct(wd)
+    import ctypes as C
+    oh = L.orc_nsnet2_new(sr, C.byref(ws))
+    for k in range(3):
+        seg = x[k * chunk:(k + 1) * chunk]
+        got = ns.denoise(seg[:5000], seg[5000:])
+        ref = np.empty(chunk, np.float32)
+        assert L.orc_nsnet2_denoise(oh, po.f32p(np.ascontiguousarray(seg)), chunk, po.f32p(ref)) == 0
+        assert np.abs(got - ref).max() < REL * np.abs(ref).max()
+    with pytest.raises(fv.FvadError) as e:
+        ns.denoise(x[:100])
+    assert e.value.name == "InvalidInputLength"
+    L.orc_nsnet2_free(oh)
+    # calcSpectrogram
+    win = po.nsnet2_window()
+    a = x[:8160:1].copy()
+    got = fv.NSNet2.calc_spectrogram(a, 50, win)
+    ref = np.stack([po.rfft(a[160 * f:160 * f + 320], win) for f in range(50)])
+    assert rel_err_rows(got, ref) < 2e-6
+    # facade
+    with pytest.raises(fv.FvadError) as e:
+        fv.AudioPipeline(44100, 2, weights=wd)
+    assert e.value.name == "InvalidSampleRate"
+    with pytest.raises(fv.FvadError) as e:
+        fv.AudioPipeline(48000, 2)  # default model path: the .onnx is not shipped
+    assert e.value.name == "OnnxError"
+    p = fv.AudioPipeline(48000, 2, weights=wd)
+    assert p.push_samples([x[:30000], x[:30000]]) == 0
+    assert p.push_samples([x[:10], x[:10]]) == 30000
+    assert p.total_write_count() == 30010
+    with pytest.raises(fv.FvadError) as e:
+        p.push_samples([x[:10]])
+    assert e.value.name == "ChannelCountMismatch"
+    assert p.vad_segments() == []
