@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py -- realtime factor (audio-sec/sec) of the full STFT -> NSNet2 -> ISTFT -> band energy -> VAD
+hot path on B200, plus the STFT kernel's HBM GB/s and the NSNet2 roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]               # this repo's CUDA path
+    python bench.py --impl reference [...]                            # the reference's CPU algorithm (oracle port)
+
+A "step" is one pass of the hot path over one batch: `--streams` (20) independent mono streams of
+`--hours` (2) h each per GPU (BASELINE.json configs[2]; config 4 = the same 20 streams on each of
+N GPUs, weak scaling, no collective on the data path).  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+# algorithmic work per unit.  Unit = one NSNet2 frame hop (10 ms of one channel).
+FLOP_PER_FRAME_STEP = 2 * 2_681_000          # fc1 + 2 x (GRU W + GRU R) + fc2 + fc3 + fc4, MAC x 2
+STEPS_PER_CHUNK, FRAMES_PER_CHUNK = 54, 50   # the reference evaluates 54 rows per 50 output frames
+
+
+def stft_bytes_per_frame(D: int, with_spec: bool) -> int:
+    # read 160*D new input samples, write 161 features (+ 161 complex bins when the spectrum is materialised)
+    return 160 * D * 4 + 161 * 4 + (161 * 8 if with_spec else 0)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1400.0, "fallback"  # B200_PROFILING.md fallback figures
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # "under load": samples whose power is above the median idle-ish floor
+        thr = 0.5 * max(pw)
+        load = [s for s, p in zip(sm, pw) if p >= thr] or sm
+        return {"sm_mhz": float(np.median(load)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference pipeline, one OS thread per stream instance
+# (reference simulator.zig:221-232), NN single-threaded per channel (onnxruntime.zig:58).
+# ------------------------------------------------------------------------------------------------
+def cpu_pipeline_throughput(fv, wd, sample_rate: int, n_threads: int, seconds_each: float, repeats: int = 1):
+    from oracle import pyoracle as po
+    po.lib()
+    xs = [fv.synth.onboard_stream(9000 + i, seconds_each, 16000, 1)[0] for i in range(n_threads)]
+    if sample_rate == 48000:
+        xs = [fv.synth.expand_16k_to_48k(x) for x in xs]
+    times = []
+    nseg = 0
+    for _ in range(repeats):
+        pipes = [po.Pipeline(wd, sample_rate, 1) for _ in range(n_threads)]
+
+        def work(i):
+            pipes[i].push_samples(xs[i])  # ctypes releases the GIL for the call
+
+        th = [threading.Thread(target=work, args=(i,)) for i in range(n_threads)]
+        t0 = time.perf_counter()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        times.append(time.perf_counter() - t0)
+        nseg = sum(len(p.segments(0)) for p in pipes)
+        for p in pipes:
+            p.close()
+    audio = n_threads * seconds_each
+    return audio, times, nseg
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # rank 0 alone runs the CPU arm
+    import fvad_b200
+    fv = fvad_b200.load()
+    wd = fv.weights.synthetic(seed=1234)
+    cores = os.cpu_count() or 1
+    sec_each = args.ref_seconds
+    for _ in range(args.warmup):
+        cpu_pipeline_throughput(fv, wd, args.sample_rate, cores, min(sec_each, 10.0))
+    audio, times, _ = cpu_pipeline_throughput(fv, wd, args.sample_rate, cores, sec_each, repeats=args.steps)
+    total = sum(times)
+    value = audio * args.steps / total
+    sample = f"{cores} streams x {sec_each:.0f} s mono {args.sample_rate} Hz per step (bounded sample of the workload)"
+    out = {
+        "impl": "reference", "metric": "realtime_factor_full_pipeline", "value": value, "unit": "audio-sec/sec",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": "audio-sec/sec", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+
+
+def workload_config(args):
+    return {"workload": f"full pipeline (STFT->NSNet2 GRU->ISTFT->band energy->VAD), {args.streams} streams x "
+                        f"{args.hours:g} h per GPU, mono {args.sample_rate} Hz, synthetic NSNet2-baseline-shaped weights",
+            "streams_per_gpu": args.streams, "hours": args.hours, "sample_rate": args.sample_rate,
+            "nn_mode": args.nn_mode, "cache": "inputs (>= 9 GB per GPU) larger than L2; no flush needed",
+            "parallelism": f"stream-sharded x{args.gpus}, no collective"}
+
+
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+    import fvad_b200
+    fv = fvad_b200.load()
+    capi = fv.capi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sr = args.sample_rate
+    D = sr // 16000
+    S = args.streams
+    seconds = args.hours * 3600.0
+    chunk = 8000 * D
+    wd = fv.weights.synthetic(seed=1234)
+    nn_mode = {"f32": capi.NN_F32, "f16x3": capi.NN_TC_F16X3, "f16": capi.NN_TC_F16}[args.nn_mode]
+
+    # ---- synthetic input, resident in HBM (and, for e2e, in pinned host memory) ----
+    seeds = [1000 * (rank + 1) + s for s in range(S)]
+    x16, labels = fv.synth.onboard_batch_torch(seeds, seconds, 16000, f"cuda:{local}")
+    if D == 3:
+        x = torch.empty((S, x16.shape[1] * 3), dtype=torch.float32, device=x16.device)
+        nxt = torch.cat([x16[:, 1:], x16[:, -1:]], dim=1)
+        x[:, 0::3] = x16
+        x[:, 1::3] = x16 + (nxt - x16) * (1.0 / 3.0)
+        x[:, 2::3] = x16 + (nxt - x16) * (2.0 / 3.0)
+        del nxt, x16
+    else:
+        x = x16
+    n = x.shape[1]
+    n_chunks = n // chunk
+    audio_sec_per_step = S * n_chunks * chunk / sr  # only whole chunks are processed (VADPipeline.zig:150)
+    dev_ptrs = [x[s].data_ptr() for s in range(S)]
+
+    gp = fv.BatchPipeline(S, sr, 1, wd, nn_mode=nn_mode, device=local)
+    clocks = ClockSampler(local)
+
+    # ---- device-resident arm ----
+    for _ in range(args.warmup):
+        gp.push_pointers(dev_ptrs, n, on_device=True)
+    st0 = gp.stats()
+    barrier()
+    clocks.start()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    stage = np.zeros(5)
+    for _ in range(args.steps):
+        gp.push_pointers(dev_ptrs, n, on_device=True)
+        st = gp.stats()
+        dev_ms += st["last_push_device_ms"]
+        stage += [st["last_stft_ms"], st["last_nn_ms"], st["last_istft_ms"], st["last_vadfft_ms"], st["last_scan_ms"]]
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    clk = clocks.stop()
+    st1 = gp.stats()
+    launches = st1["kernel_launches"] - st0["kernel_launches"]
+    n_segments = sum(len(gp.segments(s)) for s in range(S))
+
+    # ---- end-to-end arm: host (pinned) PCM in, segments out, through the C ABI ----
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    xh = torch.empty((S, n), dtype=torch.float32, pin_memory=True)
+    xh.copy_(x)
+    torch.cuda.synchronize()
+    host_ptrs = [xh[s].data_ptr() for s in range(S)]
+    gp2 = fv.BatchPipeline(S, sr, 1, wd, nn_mode=nn_mode, device=local)
+    gp2.push_pointers(host_ptrs, n, on_device=False)  # warm-up (allocations)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        gp2.push_pointers(host_ptrs, n, on_device=False)
+        segs = [gp2.segments(s) for s in range(S)]
+    barrier()
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / e2e_steps
+    d2h = sum(len(sg) for sg in segs) * 24 + S * 128
+    gp2.close()
+
+    # max over ranks
+    tt = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, e2e_ms = [float(v) for v in tt.tolist()]
+
+    if rank == 0:
+        hbm_peak, tf_peak, which = measured_peaks()
+        ms_step = dev_ms / args.steps
+        value = world * audio_sec_per_step / (ms_step * 1e-3)
+        frames = S * n_chunks * FRAMES_PER_CHUNK
+        nn_flop = S * n_chunks * STEPS_PER_CHUNK * FLOP_PER_FRAME_STEP
+        nn_ms = stage[1] / args.steps
+        stft_ms = stage[0] / args.steps
+        ach_tf = nn_flop / (nn_ms * 1e-3) / 1e12 if nn_ms > 0 else 0.0
+        sb = frames * stft_bytes_per_frame(D, True)
+        ach_gbs = sb / (stft_ms * 1e-3) / 1e9 if stft_ms > 0 else 0.0
+        out = {
+            "metric": "realtime_factor_full_pipeline", "value": value, "unit": "audio-sec/sec", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "wall_ms_per_step": wall_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"f32": "f32", "f16x3": "f16x3-split (fp32 accumulate)", "f16": "f16 (fp32 accumulate)"}[args.nn_mode],
+            "data": "synthetic", "config": workload_config(args),
+            "stage_ms_per_step": {k: float(v) / args.steps for k, v in zip(["stft", "nsnet2", "istft", "vadfft", "vadscan"], stage)},
+            "roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
+                         "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,
+                         "peak_source": f"{which} bf16_tflops_sustained"},
+            "stft_roofline": {"kernel": "stft_kernel", "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
+                              "frac": ach_gbs / hbm_peak, "traffic": None, "bytes_per_frame": stft_bytes_per_frame(D, True),
+                              "peak_source": f"{which} hbm_gbs"},
+            "e2e": {"value": world * audio_sec_per_step / (e2e_ms * 1e-3), "unit": "audio-sec/sec",
+                    "h2d_bytes_per_step": int(S * n * 4), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
+                    "steps": e2e_steps},
+            "gpu_launches": int(launches), "segments_found": int(n_segments), "clocks": clk,
+        }
+        # CPU baseline on a bounded sample (N=1 only)
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            audio, times, _ = cpu_pipeline_throughput(fv, wd, sr, cores, args.cpu_seconds)
+            out["cpu_baseline"] = {"value": audio / times[0], "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                                   "sample": f"{cores} streams x {args.cpu_seconds:.0f} s, one thread per stream (oracle port of the "
+                                             f"reference pipeline; reference binary unavailable: no zig/onnxruntime on this box)"}
+        print(json.dumps(out), flush=True)
+    gp.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--streams", type=int, default=20)
+    ap.add_argument("--hours", type=float, default=2.0)
+    ap.add_argument("--sample-rate", type=int, default=16000, choices=[16000, 48000])
+    ap.add_argument("--nn-mode", default="f32", choices=["f32", "f16x3", "f16"])
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-seconds", type=float, default=200.0)
+    ap.add_argument("--ref-seconds", type=float, default=120.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "native":
+        print("bench.py: warning: W < 3 warm-up steps breaks the timing rules", file=sys.stderr)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

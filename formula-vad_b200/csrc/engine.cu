@@ -3,6 +3,7 @@
 #include "ops.cuh"
 
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstring>
 
@@ -160,6 +161,7 @@ Batch::~Batch() {
     if (stream_) cudaStreamSynchronize(stream_);
     tables_.release();
     for (auto &e : ev_) if (e) cudaEventDestroy(e);
+    for (auto &sp : span_ev_) for (auto &e : sp) cudaEventDestroy(e);
     if (stream_) cudaStreamDestroy(stream_);
 }
 
@@ -179,6 +181,14 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
         y16_.ensure((size_t)SC_ * ypitch);
     }
     cudaStream_t s = stream_;
+
+    // per-span stage events (summed over the push's spans after the final synchronise)
+    if (span_idx_ >= span_ev_.size()) {
+        std::array<cudaEvent_t, 6> e{};
+        for (auto &x : e) FVAD_CUDA_CHECK(cudaEventCreate(&x));
+        span_ev_.push_back(e);
+    }
+    cudaEvent_t *ev_ = span_ev_[span_idx_++].data();
 
     // ---- K1 ----
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[0], s));
@@ -318,6 +328,7 @@ void Batch::push(const float *const *pcm, size_t n_pointers, size_t n, int memor
         taps_.met.ensure(std::max<size_t>((size_t)S_ * taps_.cap_vad, 1));
     }
 
+    span_idx_ = 0;
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[6], s));
     if (Ktot > 0) {
         const bool zero_copy = (memory == 1 && n_pend_ == 0);
@@ -376,10 +387,12 @@ done:
     last_ms_[0] = ms;
     if (Ktot > 0) {
         const int last = opt_.stft_only ? 1 : 5;
-        for (int i = 0; i < last; ++i) {
-            cudaEventElapsedTime(&ms, ev_[i], ev_[i + 1]);
-            last_ms_[1 + i] = ms;
-        }
+        for (int i = 0; i < 5; ++i) last_ms_[1 + i] = 0;
+        for (size_t sp = 0; sp < span_idx_; ++sp)
+            for (int i = 0; i < last; ++i) {
+                cudaEventElapsedTime(&ms, span_ev_[sp][i], span_ev_[sp][i + 1]);
+                last_ms_[1 + i] += ms;
+            }
     }
     if (segment_overflow_) throw Error(FVAD_ERR_OUT_OF_MEMORY, "segment buffer overflow (more segments than max_segments)");
 }

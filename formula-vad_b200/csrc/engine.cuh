@@ -7,6 +7,7 @@
 // passes is the halo set of SURVEY App. B (160 input samples, 4 feature rows, 160 output samples,
 // 1024 denoised samples, one chunk ratio, the VAD machine states).
 #pragma once
+#include <array>
 #include <memory>
 #include <vector>
 
@@ -47,6 +48,8 @@ private:
     int Kmax_;
     cudaStream_t stream_ = nullptr;
     cudaEvent_t ev_[8] = {};
+    std::vector<std::array<cudaEvent_t, 6>> span_ev_;  // per-span stage boundaries of the current push
+    size_t span_idx_ = 0;
     Tables tables_;
     std::unique_ptr<NnBackend> nn_;
     std::vector<MachineDerived> machines_;

@@ -181,7 +181,7 @@ typedef struct fvad_batch_stats {
     uint64_t chunks_processed; /* stream-channel chunks */
     uint64_t vad_frames;       /* per stream */
     double last_push_device_ms;/* CUDA-event time of the last push, H2D/D2H included when host memory */
-    double last_stft_ms, last_nn_ms, last_istft_ms, last_vadfft_ms, last_scan_ms; /* per-stage, last push */
+    double last_stft_ms, last_nn_ms, last_istft_ms, last_vadfft_ms, last_scan_ms; /* per-stage CUDA-event time, summed over the spans of the last push */
 } fvad_batch_stats;
 
 typedef enum fvad_tap {

@@ -140,7 +140,9 @@ def test_dsp_parity_with_forced_gains_is_tight(fv, po, wd):
         assert np.abs(d_gpu - d_ref).max() < 2e-6 * max(np.abs(d_ref).max(), 1e-3)
     band, ratio, met = op.frames()
     assert np.abs(gp.tap(fv.capi.TAP_BAND)[0] - band).max() < 5e-6 * np.abs(band).max()
-    assert np.abs(gp.tap(fv.capi.TAP_RATIO)[0] - ratio).max() < 1e-6
+    # the reference sums 24 000 squares sequentially in f32 (audio_utils.zig:14-24); the GPU tree-reduces, so
+    # the chunk RMS differs by f32 summation-order rounding (~1e-6 relative)
+    assert np.abs(gp.tap(fv.capi.TAP_RATIO)[0] - ratio).max() < 1e-5
     assert (gp.tap(fv.capi.TAP_MET)[0] == met).all()
     assert gp.segments(0) == op.segments(0) or _segments_close(gp.segments(0), op.segments(0), 0)
 
