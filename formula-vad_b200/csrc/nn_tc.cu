@@ -1,0 +1,188 @@
+// nn_tc.cu -- NSNet2 on the 5th-generation tensor cores: host side of the tcgen05 backend.
+// Weight pre-tiling (fp16 core-matrix images, GRU gate rows re-ordered so that one 48-row chunk holds
+// z|r|n of 16 units), the per-sub-batch schedule
+//     pack -> fc1 -> W1 x -> GRU1 -> W2 h1 -> GRU2 -> fc2 -> fc3 -> fc4 (gains scatter)
+// and the activation workspace.  Kernels: nn_tc_gemm.cu, nn_tc_gru.cu.
+#include <algorithm>
+#include <cstring>
+
+#include "nn.cuh"
+#include "nn_tc.cuh"
+
+namespace fvad {
+
+namespace tc {
+
+// ---- pack kernel: features f32 -> fp16 tiles -------------------------------------------------
+__global__ void __launch_bounds__(256) tc_pack_kernel(const PackArgs a) {
+    // one CTA per (q, t) tile: 128 rows x 176 columns
+    const int q = blockIdx.x / kSteps, t = blockIdx.x % kSteps;
+    uint8_t *tile = reinterpret_cast<uint8_t *>(a.A0) + (size_t)blockIdx.x * tile_bytes(176);
+    // thread -> (row, core-column): 128 rows x 22 core-columns, 16 B each
+    for (int i = threadIdx.x; i < kTileM * 22; i += blockDim.x) {
+        const int row = i % kTileM, cc = i / kTileM;
+        const int g = a.seq0 + q * kTileM + row;
+        uint4 out = make_uint4(0, 0, 0, 0);
+        if (g < a.n_seq) {
+            const int sc = g / a.Kchunks, j = g % a.Kchunks;
+            const float *src = a.feat + ((size_t)sc * (kCtx + kFrames * a.Kchunks) + (size_t)kFrames * j + t) * kBins + cc * 8;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = (cc * 8 + e < kBins) ? __ldg(src + e) : 0.0f;
+            __half2 h0 = __floats2half2_rn(v[0], v[1]), h1 = __floats2half2_rn(v[2], v[3]);
+            __half2 h2 = __floats2half2_rn(v[4], v[5]), h3 = __floats2half2_rn(v[6], v[7]);
+            out.x = *reinterpret_cast<uint32_t *>(&h0); out.y = *reinterpret_cast<uint32_t *>(&h1);
+            out.z = *reinterpret_cast<uint32_t *>(&h2); out.w = *reinterpret_cast<uint32_t *>(&h3);
+        }
+        *reinterpret_cast<uint4 *>(tile + (size_t)cc * (kTileM * 16) + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16) = out;
+    }
+}
+
+void launch_tc_pack(const PackArgs &a, cudaStream_t s) {
+    if (a.Q <= 0) return;
+    tc_pack_kernel<<<(unsigned)(a.Q * kSteps), 256, 0, s>>>(a);
+    FVAD_LAUNCHED();
+    FVAD_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace tc
+
+namespace {
+
+using tc::GemmArgs;
+
+struct Layer {  // one dense layer prepared for launch_tc_gemm
+    DevBuf<__half> img;
+    DevBuf<float> bias;
+    int K = 0, Nc = 0, n_valid = 0, n_tiles = 0;
+    int nt_size[tc::kMaxNTiles] = {}, nt_col[tc::kMaxNTiles] = {};
+    unsigned nt_off[tc::kMaxNTiles] = {};
+};
+
+// Build the fp16 image of W [N][Kin] (row-major f32) with rows taken in the order perm[] (size
+// n_valid; nullptr = identity), padded to the N-tiles `tiles` and to Kp columns.
+void build_layer(Layer &L, const float *W, const float *bias, const int *perm, int n_valid, int Kin, int Kp,
+                 const std::vector<int> &tiles) {
+    L.K = Kp; L.n_valid = n_valid; L.n_tiles = (int)tiles.size();
+    int col = 0; size_t off = 0;
+    for (size_t j = 0; j < tiles.size(); ++j) {
+        L.nt_size[j] = tiles[j]; L.nt_col[j] = col; L.nt_off[j] = (unsigned)off;
+        col += tiles[j]; off += (size_t)tiles[j] * Kp * 2;
+    }
+    L.Nc = col;
+    std::vector<__half> img(off / 2, __float2half(0.0f));
+    std::vector<float> b((size_t)L.Nc, 0.0f);
+    for (size_t j = 0; j < tiles.size(); ++j) {
+        const int NT = tiles[j];
+        uint8_t *base = reinterpret_cast<uint8_t *>(img.data()) + L.nt_off[j];
+        for (int n = 0; n < NT; ++n) {
+            const int p = L.nt_col[j] + n;
+            if (p >= n_valid) continue;
+            const int src = perm ? perm[p] : p;
+            if (bias) b[(size_t)p] = bias[src];
+            for (int k = 0; k < Kin; ++k)
+                *reinterpret_cast<__half *>(base + tc::tiled_off(n, k, NT)) = __float2half_rn(W[(size_t)src * Kin + k]);
+        }
+    }
+    L.img.ensure(img.size());
+    FVAD_CUDA_CHECK(cudaMemcpy(L.img.p, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    L.bias.ensure(b.size());
+    FVAD_CUDA_CHECK(cudaMemcpy(L.bias.p, b.data(), b.size() * sizeof(float), cudaMemcpyHostToDevice));
+}
+
+class NnTc final : public NnBackend {
+public:
+    NnTc(const HostWeights &w, bool split3) {
+        if (split3) throw Error(FVAD_ERR_INVALID_ARGUMENT, "FVAD_NN_TC_F16X3 is not built yet; use FVAD_NN_F32 for the 1e-4 gate");
+        if (w.hidden != 400 || w.n_bins != 161 || w.fc2 != 600 || w.fc3 != 600)
+            throw Error(FVAD_ERR_MODEL, "the tensor-core backend is specialised for the NSNet2-baseline shapes (161/400/600/600)");
+        int dev = 0;
+        FVAD_CUDA_CHECK(cudaGetDevice(&dev));
+        FVAD_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
+        fc1_relu_ = w.fc1_relu;
+        const int H = 400;
+        // gate-row permutation: p = 48c + 16g + u  <-  g*400 + 16c + u
+        std::vector<int> perm(3 * H);
+        for (int c = 0; c < 25; ++c)
+            for (int g = 0; g < 3; ++g)
+                for (int u = 0; u < 16; ++u) perm[(size_t)(48 * c + 16 * g + u)] = g * H + 16 * c + u;
+        build_layer(fc1_, w.fc1_w.data(), w.fc1_b.data(), nullptr, H, 161, 176, {208, 192});
+        for (int l = 0; l < 2; ++l) {
+            // xp bias: Wb + Rb for z and r; Wb alone for n (Rb_n is applied inside r*(.), nn_tc_gru.cu)
+            std::vector<float> b(3 * H);
+            for (int i = 0; i < 3 * H; ++i) b[(size_t)i] = w.gru_Wb[l][(size_t)i] + (i < 2 * H ? w.gru_Rb[l][(size_t)i] : 0.0f);
+            build_layer(gW_[l], w.gru_W[l].data(), b.data(), perm.data(), 3 * H, H, H, {240, 240, 240, 240, 240});
+            // R: 25 chunk images of 48 rows = one "layer" with 25 N-tiles of 48
+            Layer tmp;
+            std::vector<__half> img((size_t)3 * H * H);
+            for (int p = 0; p < 3 * H; ++p) {
+                const int c = p / 48, n = p % 48, src = perm[(size_t)p];
+                uint8_t *base = reinterpret_cast<uint8_t *>(img.data()) + (size_t)c * 48 * H * 2;
+                for (int k = 0; k < H; ++k)
+                    *reinterpret_cast<__half *>(base + tc::tiled_off(n, k, 48)) = __float2half_rn(w.gru_R[l][(size_t)src * H + k]);
+            }
+            gR_[l].ensure(img.size());
+            FVAD_CUDA_CHECK(cudaMemcpy(gR_[l].p, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+            gRbn_[l].ensure((size_t)H);
+            FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
+        }
+        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, {208, 208, 192});
+        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, {208, 208, 192});
+        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, {176});
+    }
+    const char *name() const override { return "tcgen05-f16"; }
+
+    void forward(const NnSpan &sp, cudaStream_t s) override {
+        const int total = sp.SC * sp.K;
+        const int q_total = (total + tc::kTileM - 1) / tc::kTileM;
+        const int QB = std::min(q_total, 2 * n_sm_);  // tiles per sub-batch
+        a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
+        x1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
+        xp_.ensure((size_t)QB * kSteps * tc::tile_bytes(1200) / 2);
+        h1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
+        h2_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
+        f2_.ensure((size_t)QB * kFrames * tc::tile_bytes(608) / 2);
+        f3_.ensure((size_t)QB * kFrames * tc::tile_bytes(608) / 2);
+        for (int q0 = 0; q0 < q_total; q0 += QB) {
+            const int Q = std::min(QB, q_total - q0);
+            tc::PackArgs pa{sp.feat, a0_.p, Q, q0 * tc::kTileM, total, sp.K};
+            tc::launch_tc_pack(pa, s);
+            gemm(fc1_, a0_.p, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
+            gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
+            tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[0].p, gRbn_[0].p, h1_.p, Q, 0}, n_sm_, s);
+            gemm(gW_[1], h1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
+            tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[1].p, gRbn_[1].p, h2_.p, Q, kCtx}, n_sm_, s);
+            gemm(fc2_, h2_.p, f2_.p, Q, kFrames, kSteps, kCtx, kFrames, 0, 1, s);
+            gemm(fc3_, f2_.p, f3_.p, Q, kFrames, kFrames, 0, kFrames, 0, 1, s);
+            GemmArgs g = base_args(fc4_, f3_.p, nullptr, Q, kFrames, kFrames, 0, kFrames, 0, 2);
+            g.out_mode = 1; g.gains = sp.gains; g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
+            tc::launch_tc_gemm(g, n_sm_, s);
+        }
+    }
+
+private:
+    int n_sm_ = 148, fc1_relu_ = 0;
+    Layer fc1_, gW_[2], fc2_, fc3_, fc4_;
+    DevBuf<__half> gR_[2];
+    DevBuf<float> gRbn_[2];
+    DevBuf<__half> a0_, x1_, xp_, h1_, h2_, f2_, f3_;
+
+    static GemmArgs base_args(const Layer &L, const __half *A, __half *C, int Q, int T, int A_q, int A_t0, int C_q, int C_t0, int act) {
+        GemmArgs g;
+        memset(&g, 0, sizeof(g));
+        g.A = A; g.B = L.img.p; g.bias = L.bias.p; g.C = C;
+        g.K = L.K; g.Nc = L.Nc; g.n_valid = L.n_valid; g.n_tiles = L.n_tiles;
+        for (int j = 0; j < L.n_tiles; ++j) { g.nt_size[j] = L.nt_size[j]; g.nt_col[j] = L.nt_col[j]; g.nt_off[j] = L.nt_off[j]; }
+        g.mt_count = Q * T; g.T = T; g.A_q = A_q; g.A_t0 = A_t0; g.C_q = C_q; g.C_t0 = C_t0; g.act = act;
+        return g;
+    }
+    void gemm(const Layer &L, const __half *A, __half *C, int Q, int T, int A_q, int A_t0, int C_q, int C_t0, int act, cudaStream_t s) {
+        tc::launch_tc_gemm(base_args(L, A, C, Q, T, A_q, A_t0, C_q, C_t0, act), n_sm_, s);
+    }
+};
+
+}  // namespace
+
+std::unique_ptr<NnBackend> make_nn_tc(const HostWeights &w, bool split3) { return std::make_unique<NnTc>(w, split3); }
+
+}  // namespace fvad

@@ -1,0 +1,66 @@
+// nn_tc.cuh -- kernel argument blocks of the tcgen05 NSNet2 backend (nn_tc.cu, nn_tc_gemm.cu, nn_tc_gru.cu).
+#pragma once
+#include "common.cuh"
+
+#include <cuda_fp16.h>
+
+namespace fvad {
+namespace tc {
+
+constexpr int kTileM = 128;            // rows (sequences) per M-tile = TMEM lanes
+constexpr int kMaxNTiles = 8;
+
+// bytes of one activation tile of `cols` columns (cols % 16 == 0) in the core-matrix tiled layout
+__host__ __device__ constexpr size_t tile_bytes(int cols) { return (size_t)kTileM * cols * 2; }
+// byte offset of element (row, col) inside a tile of R rows
+__host__ __device__ constexpr size_t tiled_off(int row, int col, int R) {
+    return (size_t)(col >> 3) * (R * 16) + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16 + (size_t)(col & 7) * 2;
+}
+
+// C = act(A * B^T + bias) over M-tiles of 128 rows.
+//   A: activation tiles, K columns.  M-tile mt -> (q = mt / T, t = mt % T); A tile index = q*A_q + t + A_t0.
+//   B: weight image: for N-tile j (nt_size[j] rows) a contiguous block at B + nt_off[j] bytes, tiled with R = nt_size[j].
+//   out_mode 0: C tiles of Nc columns (fp16), tile index q*C_q + t + C_t0, N-tile j at column nt_col[j].
+//   out_mode 1: gains scatter (f32 row-major [sc][50K][161]), frame-in-chunk = t + C_t0, columns < n_valid.
+struct GemmArgs {
+    const __half *A;
+    const __half *B;
+    const float *bias;  // [Nc]
+    __half *C;
+    float *gains;
+    int K, Nc, n_valid;
+    int n_tiles;
+    int nt_size[kMaxNTiles], nt_col[kMaxNTiles];
+    unsigned nt_off[kMaxNTiles];
+    int mt_count, T, A_q, A_t0, C_q, C_t0;
+    int act;       // 0 none, 1 relu, 2 sigmoid
+    int out_mode;
+    int seq0, n_seq, Kchunks;  // scatter: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
+};
+void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s);
+
+// One GRU layer over 54 steps for Q tiles of 128 sequences.
+//   xp:   tiles [q][54] of 1200 columns: W x_t + Wb (+Rb for z,r), columns in chunk-interleaved order
+//         (chunk c = units 16c..16c+15: [z(16) | r(16) | n(16)])
+//   Rimg: 25 chunk images (48 rows x 400 K, tiled with R = 48), same row order
+//   rbn:  Rb of the n gate, natural unit order [400]
+//   hout: tiles [q][54] of 400 columns (steps < t_store_min are not written)
+struct GruArgs {
+    const __half *xp;
+    const __half *Rimg;
+    const float *rbn;
+    __half *hout;
+    int Q, t_store_min;
+};
+void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
+
+// features f32 [SC][4+50K][161] -> fp16 tiles [q][54] of 176 columns for sequences seq0 .. seq0+128*Q-1
+struct PackArgs {
+    const float *feat;
+    __half *A0;
+    int Q, seq0, n_seq, Kchunks;
+};
+void launch_tc_pack(const PackArgs &a, cudaStream_t s);
+
+}  // namespace tc
+}  // namespace fvad
