@@ -81,6 +81,7 @@ void Batch::init_machines(const fvad_config &cfg) {
         d.sample_rate_f = sr_f;
         machines_[(size_t)m] = md;
         ring_pitch_ = std::max(ring_pitch_, d.n_long + d.n_short + d.n_ratio);
+        if (d.n_long < 2 * 256 + 2 || d.n_short + d.n_ratio > 64) scan_fast_ = 0;  // vadscan.cu fast-path limits
     }
     n_bands_ = (int)lo.size();
     band_lo_.ensure(lo.size());
@@ -122,7 +123,10 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
     if (opt_.device < 0 || opt_.device >= ndev) throw Error(FVAD_ERR_INVALID_ARGUMENT, "bad device ordinal");
     FVAD_CUDA_CHECK(cudaSetDevice(opt_.device));
     FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&scan_stream_, cudaStreamNonBlocking));
     for (auto &e : ev_) FVAD_CUDA_CHECK(cudaEventCreate(&e));
+    FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&scan_done_, cudaEventDisableTiming));
+    FVAD_CUDA_CHECK(cudaEventRecord(scan_done_, scan_stream_));
     tables_.build();
     launches0_ = g_kernel_launches;
 
@@ -159,6 +163,8 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
 
 Batch::~Batch() {
     if (stream_) cudaStreamSynchronize(stream_);
+    if (scan_stream_) { cudaStreamSynchronize(scan_stream_); cudaStreamDestroy(scan_stream_); }
+    if (scan_done_) cudaEventDestroy(scan_done_);
     tables_.release();
     for (auto &e : ev_) if (e) cudaEventDestroy(e);
     for (auto &sp : span_ev_) for (auto &e : sp) cudaEventDestroy(e);
@@ -184,7 +190,7 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
 
     // per-span stage events (summed over the push's spans after the final synchronise)
     if (span_idx_ >= span_ev_.size()) {
-        std::array<cudaEvent_t, 6> e{};
+        std::array<cudaEvent_t, 7> e{};
         for (auto &x : e) FVAD_CUDA_CHECK(cudaEventCreate(&x));
         span_ev_.push_back(e);
     }
@@ -227,11 +233,13 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
         launch_copy_rows(sumsq_.p, sumsq_carry_.p, (size_t)K + 1, 1, 1, (size_t)SC_, s);
         FVAD_CUDA_CHECK(cudaEventRecord(ev_[3], s));
 
-        // ---- K3b ----
+        // ---- K3b ----  (band_/ratio_/met_ are read by the previous span's scan on scan_stream_)
+        FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));
         const uint64_t frames_end = span_end / (uint64_t)fft_size_;
         n_frames = (int)(frames_end - frames_done_);
         if (n_frames > 0) {
             if (n_frames > max_frames_) {
+                FVAD_CUDA_CHECK(cudaStreamSynchronize(scan_stream_));  // the previous scan still reads the old buffers
                 max_frames_ = n_frames + 64;
                 band_.ensure((size_t)n_bands_ * S_ * max_frames_);
                 ratio_.ensure((size_t)S_ * max_frames_);
@@ -248,16 +256,20 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
         }
         FVAD_CUDA_CHECK(cudaEventRecord(ev_[4], s));
 
-        // ---- K4 ----
+        // ---- K4 ----  on its own stream: a latency-bound scan that overlaps the next span's network
+        FVAD_CUDA_CHECK(cudaStreamWaitEvent(scan_stream_, ev_[4], 0));
+        FVAD_CUDA_CHECK(cudaEventRecord(ev_[5], scan_stream_));
         if (n_frames > 0) {
             ScanArgs ca;
             ca.band = band_.p; ca.ratio = ratio_.p; ca.machines = d_machines_.p; ca.states = d_states_.p;
             ca.rings = rings_.p; ca.ring_pitch = ring_pitch_; ca.segments = d_segments_.p; ca.max_segments = max_segments_;
             ca.met = met_.p; ca.S = S_; ca.M = M_; ca.n_frames = n_frames; ca.max_frames = max_frames_;
-            ca.first_frame = (long long)frames_done_; ca.fft_size = fft_size_;
-            launch_vadscan(ca, s);
+            ca.first_frame = (long long)frames_done_; ca.fft_size = fft_size_; ca.fast = scan_fast_;
+            launch_vadscan(ca, scan_stream_);
         }
-        FVAD_CUDA_CHECK(cudaEventRecord(ev_[5], s));
+        FVAD_CUDA_CHECK(cudaEventRecord(ev_[6], scan_stream_));
+        FVAD_CUDA_CHECK(cudaEventRecord(scan_done_, scan_stream_));
+        if (opt_.keep_taps) FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));  // the taps below copy met_
     }
 
     // ---- taps ----
@@ -379,6 +391,7 @@ void Batch::push(const float *const *pcm, size_t n_pointers, size_t n, int memor
         n_pend_ = (int)total;
     }
 done:
+    FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));
     if (Ktot > 0 && !opt_.stft_only) fetch_segments();
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[7], s));
     FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
@@ -390,7 +403,8 @@ done:
         for (int i = 0; i < 5; ++i) last_ms_[1 + i] = 0;
         for (size_t sp = 0; sp < span_idx_; ++sp)
             for (int i = 0; i < last; ++i) {
-                cudaEventElapsedTime(&ms, span_ev_[sp][i], span_ev_[sp][i + 1]);
+                const int e0 = i < 4 ? i : 5, e1 = i < 4 ? i + 1 : 6;  // the scan runs on scan_stream_
+                cudaEventElapsedTime(&ms, span_ev_[sp][e0], span_ev_[sp][e1]);
                 last_ms_[1 + i] += ms;
             }
     }

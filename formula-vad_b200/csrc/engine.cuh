@@ -46,14 +46,16 @@ private:
     size_t sample_rate_;
     fvad_batch_options opt_;
     int Kmax_;
-    cudaStream_t stream_ = nullptr;
+    cudaStream_t stream_ = nullptr, scan_stream_ = nullptr;
+    cudaEvent_t scan_done_ = nullptr;
     cudaEvent_t ev_[8] = {};
-    std::vector<std::array<cudaEvent_t, 6>> span_ev_;  // per-span stage boundaries of the current push
+    std::vector<std::array<cudaEvent_t, 7>> span_ev_;  // per-span stage boundaries of the current push
     size_t span_idx_ = 0;
     Tables tables_;
     std::unique_ptr<NnBackend> nn_;
     std::vector<MachineDerived> machines_;
     int n_bands_ = 0;
+    int scan_fast_ = 1;
 
     // progress
     uint64_t total_written_ = 0;   // samples pushed per channel

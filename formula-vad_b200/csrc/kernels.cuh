@@ -89,6 +89,7 @@ struct ScanArgs {
     int S, M, n_frames, max_frames;
     long long first_frame;       // absolute frame number of column 0
     int fft_size;
+    int fast;                    // every machine has n_long >= 514 and n_short + n_ratio <= 64 (vadscan.cu)
 };
 void launch_vadscan(const ScanArgs &a, cudaStream_t s);
 

@@ -5,7 +5,7 @@
 // Replaces the MatMul/Add/Relu/Sigmoid nodes that onnxruntime executes inside
 // `onnx_instance.run()` (reference src/NSNet2.zig:220).
 //
-// Roles (256 threads): warp 0 producer (cp.async.bulk of A and B K-slabs into a 4-stage ring),
+// Roles (256 threads): warp 0 producer (cp.async.bulk: the M-tile's A slabs once, B K-slabs into a ring),
 // warp 1 MMA issuer (one elected lane, tcgen05.mma kind::f16, accumulators in TMEM, two
 // accumulator buffers of 256 columns), warp 2 TMEM allocator, warps 4..7 epilogue (tcgen05.ld ->
 // bias -> activation -> fp16 tiles for the next layer, or the f32 gains scatter).
@@ -17,28 +17,39 @@ namespace tc {
 
 namespace {
 
-constexpr int kStages = 4;
-constexpr int kSlabK = 64;                          // K columns per pipeline stage
-constexpr int kABytes = kTileM * kSlabK * 2;        // 16 KB
-constexpr int kBBytes = 256 * kSlabK * 2;           // 32 KB (N-tile <= 256)
-constexpr int kStageBytes = kABytes + kBBytes;
+// Shared memory: [A tile, all K columns | B ring: n_stages x (256 rows x KS cols max) | bias | barriers].
+// The A tile of an M-tile is fetched once (through the same producer queue, slab by slab, while the
+// first N-tile runs) and stays resident for all N-tiles, so L2 traffic per M-tile is A + the whole
+// weight matrix: 128 flop per byte, the same intensity as the GRU kernel's R stream.
+constexpr int kMaxSlabs = 20;
+constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 256;
-constexpr int kGemmSmem = kStages * kStageBytes + 1024;
+constexpr int kSmemTotal = 227 * 1024;
 
 struct GemmShared {
-    uint64_t full[kStages], empty[kStages], acc_full[2], acc_empty[2];
+    uint64_t full[kMaxStages], empty[kMaxStages], a_full[kMaxSlabs], a_empty[kMaxSlabs], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
 
-__global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs a) {
+struct GemmPlan {  // host-computed shared-memory plan
+    int KS, n_slabs, n_stages, stage_bytes, a_bytes, bias_off, sh_off, smem_bytes;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs a, const GemmPlan pl) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    GemmShared *sh = reinterpret_cast<GemmShared *>(smem + kStages * kStageBytes);
+    uint8_t *sA = smem, *sB = smem + pl.a_bytes;
+    float *bias_s = reinterpret_cast<float *>(smem + pl.bias_off);
+    GemmShared *sh = reinterpret_cast<GemmShared *>(smem + pl.sh_off);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kStages; ++i) {
+        for (int i = 0; i < pl.n_stages; ++i) {
             mbar_init(&sh->full[i], 1);
             mbar_init(&sh->empty[i], 1);
+        }
+        for (int i = 0; i < pl.n_slabs; ++i) {
+            mbar_init(&sh->a_full[i], 1);
+            mbar_init(&sh->a_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&sh->acc_full[i], 1);
@@ -46,34 +57,38 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
         }
         fence_mbar_init();
     }
+    for (int i = threadIdx.x; i < a.Nc; i += kGemmThreads) bias_s[i] = a.bias[i];
     if (warp == 2) tmem_alloc<512>(&sh->tmem_base);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = sh->tmem_base;
-
-    const int n_slabs = (a.K + kSlabK - 1) / kSlabK;
+    const int KS = pl.KS, n_slabs = pl.n_slabs, n_stages = pl.n_stages;
     const size_t a_tile_bytes = tile_bytes(a.K);
 
     if (warp == 0) {
         // ===== producer =====
         if (elect_one()) {
-            uint32_t it = 0;
-            for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x) {
+            uint32_t it = 0, st = 0, ph = 0, im = 0;
+            for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
                 const int q = mt / a.T, t = mt % a.T;
                 const uint8_t *At = reinterpret_cast<const uint8_t *>(a.A) + (size_t)(q * a.A_q + t + a.A_t0) * a_tile_bytes;
                 for (int j = 0; j < a.n_tiles; ++j) {
                     const int NT = a.nt_size[j];
                     const uint8_t *Bt = reinterpret_cast<const uint8_t *>(a.B) + a.nt_off[j];
                     for (int sl = 0; sl < n_slabs; ++sl, ++it) {
-                        const int st = it % kStages;
-                        mbar_wait(&sh->empty[st], ((it / kStages) & 1) ^ 1);
-                        const int k0 = sl * kSlabK, kw = min(kSlabK, a.K - k0);
-                        const uint32_t ab = (uint32_t)(kw / 8) * (kTileM * 16), bb = (uint32_t)(kw / 8) * (NT * 16);
-                        uint8_t *sa = smem + st * kStageBytes, *sb = sa + kABytes;
-                        mbar_expect_tx(&sh->full[st], ab + bb);
-                        bulk_g2s(sa, At + (size_t)(k0 / 8) * (kTileM * 16), ab, &sh->full[st]);
-                        bulk_g2s(sb, Bt + (size_t)(k0 / 8) * (NT * 16), bb, &sh->full[st]);
+                        const int k0 = sl * KS, kw = min(KS, a.K - k0);
+                        if (j == 0) {  // this M-tile's A slab (slot freed by the previous M-tile's last N-tile)
+                            mbar_wait(&sh->a_empty[sl], (im & 1) ^ 1);
+                            const uint32_t ab = (uint32_t)(kw / 8) * (kTileM * 16);
+                            mbar_expect_tx(&sh->a_full[sl], ab);
+                            bulk_g2s(sA + (size_t)(k0 / 8) * (kTileM * 16), At + (size_t)(k0 / 8) * (kTileM * 16), ab, &sh->a_full[sl]);
+                        }
+                        mbar_wait(&sh->empty[st], ph ^ 1);
+                        const uint32_t bb = (uint32_t)(kw / 8) * (NT * 16);
+                        mbar_expect_tx(&sh->full[st], bb);
+                        bulk_g2s(sB + (size_t)st * pl.stage_bytes, Bt + (size_t)(k0 / 8) * (NT * 16), bb, &sh->full[st]);
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                 }
             }
@@ -81,8 +96,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (elect_one()) {
-            uint32_t it = 0, work = 0;
-            for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x) {
+            uint32_t st = 0, ph = 0, work = 0, im = 0;
+            const uint32_t sa0 = smem_u32(sA), sb0 = smem_u32(sB);
+            for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
                 for (int j = 0; j < a.n_tiles; ++j, ++work) {
                     const int NT = a.nt_size[j];
                     const uint32_t buf = work & 1;
@@ -90,18 +106,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                     tc_fence_after();
                     const uint32_t idesc = make_idesc_f16(kTileM, NT);
                     const uint32_t d = tmem + buf * 256;
-                    for (int sl = 0; sl < n_slabs; ++sl, ++it) {
-                        const int st = it % kStages;
-                        mbar_wait(&sh->full[st], (it / kStages) & 1);
+                    const bool last_n = (j == a.n_tiles - 1);
+                    for (int sl = 0; sl < n_slabs; ++sl) {
+                        if (j == 0) mbar_wait(&sh->a_full[sl], im & 1);
+                        mbar_wait(&sh->full[st], ph);
                         tc_fence_after();
-                        const int kw = min(kSlabK, a.K - sl * kSlabK);
-                        const uint32_t sa = smem_u32(smem + st * kStageBytes), sb = sa + kABytes;
+                        const int k0 = sl * KS, kw = min(KS, a.K - k0);
+                        const uint32_t sa = sa0 + (k0 / 8) * (kTileM * 16), sb = sb0 + st * pl.stage_bytes;
                         for (int kk = 0; kk < kw / 16; ++kk) {
                             const uint64_t ad = make_smem_desc(sa + kk * 2 * (kTileM * 16), kTileM * 16, 128);
                             const uint64_t bd = make_smem_desc(sb + kk * 2 * (NT * 16), NT * 16, 128);
                             mma_ss(d, ad, bd, idesc, (sl > 0 || kk > 0) ? 1u : 0u);
                         }
-                        mma_commit(&sh->empty[st]);  // frees the stage when these MMAs have read it
+                        mma_commit(&sh->empty[st]);               // B stage free once these MMAs have read it
+                        if (last_n) mma_commit(&sh->a_empty[sl]); // A slab free for the next M-tile
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                     mma_commit(&sh->acc_full[buf]);
                 }
@@ -140,7 +159,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                     float v[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        float x = __uint_as_float(r[i]) + __ldg(a.bias + col0 + c + i);
+                        float x = __uint_as_float(r[i]) + bias_s[col0 + c + i];
                         if (a.act == 1) x = fmaxf(x, 0.0f);
                         else if (a.act == 2) x = __fdividef(1.0f, 1.0f + __expf(-x));
                         v[i] = x;
@@ -174,12 +193,30 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
 void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     static bool attr = false;
     if (!attr) {
-        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
         attr = true;
     }
     if (a.mt_count <= 0) return;
+    GemmPlan pl;
+    int nt_max = 0;
+    for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
+    pl.a_bytes = a.K * 256;  // K/8 core columns x 2048 B
+    const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + 1024;
+    pl.KS = 64;
+    for (;;) {
+        pl.stage_bytes = nt_max * pl.KS * 2;
+        pl.n_stages = (kSmemTotal - pl.a_bytes - fixed) / pl.stage_bytes;
+        if (pl.n_stages >= 4 || pl.KS == 16) break;
+        pl.KS /= 2;
+    }
+    if (pl.n_stages > kMaxStages) pl.n_stages = kMaxStages;
+    pl.n_slabs = (a.K + pl.KS - 1) / pl.KS;
+    if (pl.n_stages < 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: layer does not fit the shared-memory plan");
+    pl.bias_off = pl.a_bytes + pl.n_stages * pl.stage_bytes;
+    pl.sh_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
+    pl.smem_bytes = pl.sh_off + 1024;
     const int grid = a.mt_count < n_sm ? a.mt_count : n_sm;
-    tc_gemm_kernel<<<grid, kGemmThreads, kGemmSmem, s>>>(a);
+    tc_gemm_kernel<<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
 }

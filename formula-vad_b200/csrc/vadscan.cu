@@ -31,7 +31,61 @@ __device__ __forceinline__ double ring_push(double *ring, int len, int &idx, int
     return sum * (1.0 / (double)cnt);
 }
 
-__global__ void __launch_bounds__(128) vadscan_kernel(ScanArgs a) {
+// FSM + statistics of one frame, given this frame's threshold decision (VADMachine.zig:189-263)
+__device__ __forceinline__ void fsm_step(ScanState &st, const ScanMachine &mc, bool met, float meta_ratio,
+                                         unsigned long long index, fvad_segment *segs, int max_segments) {
+    const int from_state = st.state;
+    switch (st.state) {  // VADMachine.zig:189-233
+        case ST_CLOSED:
+            if (met) { st.state = ST_OPENING; st.start_index = index; }
+            break;
+        case ST_OPENING:
+            if (met && (index - st.start_index) >= mc.min_to_open) st.state = ST_OPEN;
+            else if (!met) st.state = ST_CLOSED;
+            break;
+        case ST_OPEN:
+            if (!met) { st.state = ST_CLOSING; st.end_index = index; }
+            break;
+        case ST_CLOSING:
+            if (met) st.state = ST_OPEN;
+            else if ((index - st.end_index) >= mc.max_gap) {
+                st.state = ST_CLOSED;
+                // onSpeechEnd, VADMachine.zig:265-309
+                const float len_sec = __fdiv_rn((float)(st.end_index - st.start_index), mc.sample_rate_f);
+                if (len_sec >= mc.min_duration_sec) {
+                    if (st.n_segments < (unsigned)max_segments) {
+                        fvad_segment g;
+                        const unsigned long long mg = mc.start_margin < st.start_index ? mc.start_margin : st.start_index;
+                        g.sample_from = st.start_index - mg;
+                        g.sample_to = st.end_index + mc.end_margin;
+                        g.avg_channel_vol_ratio = __fdiv_rn(st.vol_ratio_sum, (float)st.vol_ratio_count);
+                        g.vad_met_sec = st.met_sec;
+                        segs[st.n_segments] = g;
+                    }
+                    ++st.n_segments;
+                }
+            }
+            break;
+    }
+    // trackSpeechStats, VADMachine.zig:241-263
+    if (from_state == ST_CLOSED && st.state == ST_OPENING) {
+        st.vol_ratio_sum = meta_ratio;
+        st.vol_ratio_count = 1;
+        st.met_sec = mc.frame_sec;
+    } else if (from_state == ST_OPEN) {
+        st.vol_ratio_sum = __fadd_rn(st.vol_ratio_sum, meta_ratio);
+        st.vol_ratio_count += 1;
+        if (met) st.met_sec = __fadd_rn(st.met_sec, mc.frame_sec);
+    }
+}
+
+constexpr int kScanThreads = 32;
+constexpr int kSmallRing = 64;   // doubles of shared memory for the short + ratio rings (fast path)
+constexpr int kBatch = 256;      // frames staged per batch (fast path)
+constexpr int PF = 8;            // frames fetched ahead of the dependent chain (generic path)
+
+// Generic path: one thread per (stream, machine), rings in global memory.
+__global__ void __launch_bounds__(kScanThreads) vadscan_kernel(ScanArgs a) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= a.S * a.M) return;
     const int s = t / a.M, m = t % a.M;
@@ -45,7 +99,6 @@ __global__ void __launch_bounds__(128) vadscan_kernel(ScanArgs a) {
     fvad_segment *segs = a.segments + (size_t)t * a.max_segments;
     unsigned char *met_out = (a.met && m == 0) ? a.met + (size_t)s * a.max_frames : nullptr;
 
-    constexpr int PF = 8;  // frames fetched ahead of the dependent chain
     for (int i0 = 0; i0 < a.n_frames; i0 += PF) {
         float eb[PF], rb[PF];
 #pragma unroll
@@ -60,7 +113,6 @@ __global__ void __launch_bounds__(128) vadscan_kernel(ScanArgs a) {
             if (i >= a.n_frames) break;
             const float min_volume = eb[j], meta_ratio = rb[j];
             const unsigned long long index = (unsigned long long)(a.first_frame + i) * (unsigned long long)a.fft_size;
-
             // VADMachine.zig:165-178
             const double short_term = ring_push(ring_short, mc.n_short, st.short_idx, st.short_cnt, st.short_sum, min_volume);
             const double vol_ratio = ring_push(ring_ratio, mc.n_ratio, st.ratio_idx, st.ratio_cnt, st.ratio_sum, meta_ratio);
@@ -72,59 +124,136 @@ __global__ void __launch_bounds__(128) vadscan_kernel(ScanArgs a) {
                 st.has_last = 1;
             }
             if (met_out) met_out[i] = met ? 1 : 0;
-
-            const int from_state = st.state;
-            switch (st.state) {  // VADMachine.zig:189-233
-                case ST_CLOSED:
-                    if (met) { st.state = ST_OPENING; st.start_index = index; }
-                    break;
-                case ST_OPENING:
-                    if (met && (index - st.start_index) >= mc.min_to_open) st.state = ST_OPEN;
-                    else if (!met) st.state = ST_CLOSED;
-                    break;
-                case ST_OPEN:
-                    if (!met) { st.state = ST_CLOSING; st.end_index = index; }
-                    break;
-                case ST_CLOSING:
-                    if (met) st.state = ST_OPEN;
-                    else if ((index - st.end_index) >= mc.max_gap) {
-                        st.state = ST_CLOSED;
-                        // onSpeechEnd, VADMachine.zig:265-309
-                        const float len_sec = __fdiv_rn((float)(st.end_index - st.start_index), mc.sample_rate_f);
-                        if (len_sec >= mc.min_duration_sec) {
-                            if (st.n_segments < (unsigned)a.max_segments) {
-                                fvad_segment g;
-                                const unsigned long long mg = mc.start_margin < st.start_index ? mc.start_margin : st.start_index;
-                                g.sample_from = st.start_index - mg;
-                                g.sample_to = st.end_index + mc.end_margin;
-                                g.avg_channel_vol_ratio = __fdiv_rn(st.vol_ratio_sum, (float)st.vol_ratio_count);
-                                g.vad_met_sec = st.met_sec;
-                                segs[st.n_segments] = g;
-                            }
-                            ++st.n_segments;
-                        }
-                    }
-                    break;
-            }
-            // trackSpeechStats, VADMachine.zig:241-263
-            if (from_state == ST_CLOSED && st.state == ST_OPENING) {
-                st.vol_ratio_sum = meta_ratio;
-                st.vol_ratio_count = 1;
-                st.met_sec = mc.frame_sec;
-            } else if (from_state == ST_OPEN) {
-                st.vol_ratio_sum = __fadd_rn(st.vol_ratio_sum, meta_ratio);
-                st.vol_ratio_count += 1;
-                if (met) st.met_sec = __fadd_rn(st.met_sec, mc.frame_sec);
-            }
+            fsm_step(st, mc, met, meta_ratio, index, segs, a.max_segments);
         }
     }
     a.states[t] = st;
 }
 
+// Fast path: one WARP per (stream, machine), frames staged through shared memory in batches.
+//   * The short-term and ratio means do not depend on the recurrence: all lanes evaluate them in
+//     parallel, each as the reference does -- the array-order sum of data[i] * (1/written)
+//     (RollingAverage.zig:45-56) -- from a chronological history kept in shared memory, so these two
+//     means are bit-identical to the reference's.  (In this mode the short/ratio ring storage holds
+//     the last n-1 pushed values in chronological order instead of a circular buffer.)
+//   * The long-term mean is the true recurrence (it is only pushed on !met frames): lane 0 runs it
+//     as an f64 running sum; the next kBatch+2 eviction candidates of the long ring are staged
+//     ahead (the ring advances by at most one slot per frame and n_long >= 2*kBatch+2), so no
+//     global-memory latency sits on the chain last_avg -> threshold -> met -> long sum -> last_avg.
+__device__ __forceinline__ double window_mean(const float *newest, int n, int pm, int cnt) {
+    // data[] position i holds the value pushed r = (pm - i) mod n pushes ago; sum in array order
+    const double scalar = 1.0 / (double)cnt;
+    double acc = 0.0;
+    for (int i = 0; i < cnt; ++i) {
+        int r = pm - i;
+        if (r < 0) r += n;
+        acc = __dadd_rn(acc, __dmul_rn((double)newest[-r], scalar));
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) {
+    __shared__ float s_rb[kBatch];
+    __shared__ double s_lw[kBatch + 2], s_st[kBatch], s_vr[kBatch];
+    __shared__ float x_s[kSmallRing + kBatch], x_r[kSmallRing + kBatch];  // [n-1 history | batch], chronological
+    const int t = blockIdx.x, lane = threadIdx.x;
+    const int s = t / a.M, m = t % a.M;
+    const ScanMachine mc = a.machines[m];
+    ScanState st = a.states[t];
+    double *ring_long = a.rings + (size_t)t * a.ring_pitch;
+    double *ring_short = ring_long + mc.n_long;
+    double *ring_ratio = ring_short + mc.n_short;
+    const float *__restrict__ band = a.band + ((size_t)mc.band * a.S + s) * a.max_frames;
+    const float *__restrict__ ratio = a.ratio + (size_t)s * a.max_frames;
+    fvad_segment *segs = a.segments + (size_t)t * a.max_segments;
+    unsigned char *met_out = (a.met && m == 0) ? a.met + (size_t)s * a.max_frames : nullptr;
+    const int hs = mc.n_short - 1, hr = mc.n_ratio - 1;
+    for (int k = lane; k < hs; k += 32) x_s[k] = (float)ring_short[k];
+    for (int k = lane; k < hr; k += 32) x_r[k] = (float)ring_ratio[k];
+    double inv_long = 1.0 / (double)(st.long_cnt > 0 ? st.long_cnt : 1);
+    unsigned long long index = (unsigned long long)a.first_frame * (unsigned long long)a.fft_size;
+
+    for (int i0 = 0; i0 < a.n_frames; i0 += kBatch) {
+        const int nb = min(kBatch, a.n_frames - i0);
+        const int lidx = __shfl_sync(0xffffffffu, st.long_idx, 0);
+        for (int j = lane; j < nb; j += 32) {
+            x_s[hs + j] = band[i0 + j];
+            const float r = ratio[i0 + j];
+            x_r[hr + j] = r;
+            s_rb[j] = r;
+        }
+        for (int j = lane; j < nb + 2; j += 32) {
+            int li = lidx + j;
+            if (li >= mc.n_long) li -= mc.n_long;
+            s_lw[j] = ring_long[li];
+        }
+        __syncwarp();
+        for (int j = lane; j < nb; j += 32) {
+            s_st[j] = window_mean(x_s + hs + j, mc.n_short, (st.short_idx + j) % mc.n_short, min(st.short_cnt + j + 1, mc.n_short));
+            s_vr[j] = window_mean(x_r + hr + j, mc.n_ratio, (st.ratio_idx + j) % mc.n_ratio, min(st.ratio_cnt + j + 1, mc.n_ratio));
+        }
+        __syncwarp();
+        if (lane == 0) {
+            int k = 0;
+            double cur = s_lw[0], nxt = s_lw[1];
+#pragma unroll 2
+            for (int j = 0; j < nb; ++j) {
+                const float min_volume = x_s[hs + j], meta_ratio = s_rb[j];
+                const double short_term = s_st[j], vol_ratio = s_vr[j];
+                // VADMachine.zig:165-178
+                const double base = st.has_last ? st.last_avg : (mc.has_init ? mc.init_avg : short_term);
+                const double threshold = base * mc.threshold_factor;
+                const bool met = (short_term > threshold) && (vol_ratio > mc.ratio_threshold);
+                if (!met) {
+                    const double nv = (double)min_volume;
+                    const double old = (st.long_cnt == mc.n_long) ? cur : 0.0;
+                    st.long_sum = (st.long_sum - old) + nv;
+                    ring_long[st.long_idx] = nv;
+                    st.long_idx = (st.long_idx + 1 == mc.n_long) ? 0 : st.long_idx + 1;
+                    if (st.long_cnt < mc.n_long) {
+                        ++st.long_cnt;
+                        inv_long = 1.0 / (double)st.long_cnt;
+                    }
+                    st.last_avg = st.long_sum * inv_long;
+                    st.has_last = 1;
+                    ++k;
+                    cur = nxt;
+                    nxt = s_lw[k + 1];
+                }
+                if (met_out) met_out[i0 + j] = met ? 1 : 0;
+                if (met || st.state != ST_CLOSED)  // closed and not met: nothing changes (VADMachine.zig:190-196)
+                    fsm_step(st, mc, met, meta_ratio, index, segs, a.max_segments);
+                index += (unsigned long long)a.fft_size;
+            }
+        }
+        // ring counters advance identically on every lane; histories shift by nb
+        st.short_idx = (st.short_idx + nb) % mc.n_short;
+        st.short_cnt = min(st.short_cnt + nb, mc.n_short);
+        st.ratio_idx = (st.ratio_idx + nb) % mc.n_ratio;
+        st.ratio_cnt = min(st.ratio_cnt + nb, mc.n_ratio);
+        __syncwarp();
+        float v0 = 0.f, v1 = 0.f, w0 = 0.f, w1 = 0.f;
+        if (lane < hs) v0 = x_s[nb + lane];
+        if (lane + 32 < hs) v1 = x_s[nb + lane + 32];
+        if (lane < hr) w0 = x_r[nb + lane];
+        if (lane + 32 < hr) w1 = x_r[nb + lane + 32];
+        __syncwarp();
+        if (lane < hs) x_s[lane] = v0;
+        if (lane + 32 < hs) x_s[lane + 32] = v1;
+        if (lane < hr) x_r[lane] = w0;
+        if (lane + 32 < hr) x_r[lane + 32] = w1;
+        __syncwarp();
+    }
+    for (int k = lane; k < hs; k += 32) ring_short[k] = (double)x_s[k];
+    for (int k = lane; k < hr; k += 32) ring_ratio[k] = (double)x_r[k];
+    if (lane == 0) a.states[t] = st;
+}
+
 void launch_vadscan(const ScanArgs &a, cudaStream_t s) {
     if (a.n_frames <= 0) return;
     const int total = a.S * a.M;
-    vadscan_kernel<<<(total + 127) / 128, 128, 0, s>>>(a);
+    if (a.fast) vadscan_warp_kernel<<<(unsigned)total, kScanThreads, 0, s>>>(a);
+    else vadscan_kernel<<<(unsigned)((total + kScanThreads - 1) / kScanThreads), kScanThreads, 0, s>>>(a);
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
 }
