@@ -5,5 +5,5 @@ helper `fvad_b200.py`, which registers this package as `formula_vad_b200`.
 The compute lives in csrc/ (hand-written sm_100a CUDA behind the C ABI of include/fvad.h);
 this package is the thin host-side mirror of the reference's AudioPipeline / FFT / NSNet2 surface.
 """
-from . import capi, synth, weights  # noqa: F401
+from . import capi, sharding, synth, weights  # noqa: F401
 from .pipeline import FFT, NSNet2, AudioPipeline, BatchPipeline, FvadError, vad_machine_config  # noqa: F401

@@ -97,6 +97,16 @@ class EvalStats(C.Structure):
                                           "fdr", "f_score", "fm")]
 
 
+class Meta(C.Structure):  # AudioPipeline/VADMetadata.zig accumulator
+    _fields_ = [("has_ratio", C.c_int), ("ratio_sum", C.c_float), ("ratio_weight", C.c_float),
+                ("has_min", C.c_int), ("vmin", C.c_float), ("has_max", C.c_int), ("vmax", C.c_float)]
+
+
+class MetaResult(C.Structure):
+    _fields_ = [("has_ratio", C.c_int), ("ratio", C.c_float), ("has_min", C.c_int), ("vmin", C.c_float),
+                ("has_max", C.c_int), ("vmax", C.c_float)]
+
+
 def build(force: bool = False) -> None:
     """Compile the oracle (and oracle/_ref when the reference checkout is present)."""
     if force or not os.path.exists(LIB_PATH) or any(
@@ -154,6 +164,9 @@ def lib():
     sig("orc_rolling_new", vp, C.c_size_t, C.c_int, C.c_double)
     sig("orc_rolling_free", None, vp)
     sig("orc_rolling_push", C.c_double, vp, C.c_float)
+    sig("orc_meta_push", None, C.POINTER(Meta), C.POINTER(MetaResult), C.c_float)
+    sig("orc_meta_to_result", MetaResult, C.POINTER(Meta))
+    sig("orc_downsample", None, c_f32p, C.c_size_t, c_f32p, C.c_int)
     sig("orc_vadm_new", vp, C.POINTER(VadMachineConfig), C.c_size_t, C.c_size_t, C.c_size_t)
     sig("orc_vadm_free", None, vp)
     sig("orc_vadm_run", C.c_int, vp, c_f32p, C.c_uint64, C.c_int, C.c_float, C.POINTER(C.c_uint64))
