@@ -76,7 +76,7 @@ EXPORTS = (
     "fvad_nsnet2_calc_spectrogram", "fvad_pipeline_create", "fvad_pipeline_create_with_weights",
     "fvad_pipeline_destroy", "fvad_pipeline_push_samples", "fvad_pipeline_total_write_count",
     "fvad_pipeline_segments", "fvad_batch_options_default", "fvad_batch_create", "fvad_batch_destroy",
-    "fvad_batch_push", "fvad_batch_segments", "fvad_batch_tap", "fvad_batch_stats_get",
+    "fvad_batch_push", "fvad_batch_push_i16", "fvad_batch_segments", "fvad_batch_tap", "fvad_batch_stats_get",
 )
 
 
@@ -135,6 +135,7 @@ def lib():
     sig("fvad_batch_create", i32, sz, C.POINTER(Config), C.POINTER(Weights), C.POINTER(BatchOptions), C.POINTER(vp))
     sig("fvad_batch_destroy", None, vp)
     sig("fvad_batch_push", i32, vp, C.POINTER(vp), sz, sz, i32)
+    sig("fvad_batch_push_i16", i32, vp, C.POINTER(vp), sz, sz, i32)
     sig("fvad_batch_segments", i32, vp, sz, sz, C.POINTER(C.POINTER(Segment)), C.POINTER(sz))
     sig("fvad_batch_tap", i32, vp, i32, vp, sz, C.POINTER(sz))
     sig("fvad_batch_stats_get", i32, vp, C.POINTER(BatchStats))

@@ -393,6 +393,13 @@ int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n_pointers, s
     });
 }
 
+int fvad_batch_push_i16(fvad_batch *b, const int16_t *const *pcm, size_t n_pointers, size_t n, int memory) {
+    return guarded([&] {
+        if (!b) throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL handle");
+        b->impl->push_i16(pcm, n_pointers, n, memory);
+    });
+}
+
 int fvad_batch_segments(fvad_batch *b, size_t stream, size_t machine, const fvad_segment **segs, size_t *n) {
     return guarded([&] {
         if (!b) throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL handle");

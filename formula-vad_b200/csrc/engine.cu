@@ -124,6 +124,11 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
     FVAD_CUDA_CHECK(cudaSetDevice(opt_.device));
     FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
     FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&scan_stream_, cudaStreamNonBlocking));
+    FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&stage_ready_[i], cudaEventDisableTiming));
+        FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&stage_free_[i], cudaEventDisableTiming));
+    }
     for (auto &e : ev_) FVAD_CUDA_CHECK(cudaEventCreate(&e));
     FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&scan_done_, cudaEventDisableTiming));
     FVAD_CUDA_CHECK(cudaEventRecord(scan_done_, scan_stream_));
@@ -131,7 +136,11 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
     launches0_ = g_kernel_launches;
 
     // span size: bounded by memory for the per-frame intermediates (~3.2 KB per frame-row)
-    size_t kmax = opt_.max_span_chunks ? opt_.max_span_chunks : std::max<size_t>(1, 32768 / (size_t)SC_);
+    // auto: two full waves of 128-sequence GRU tiles (one CTA per SM owns a tile for all 54 steps), so the
+    // recurrent kernel never runs a partial wave except in a push's last span
+    int n_sm = 148;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, opt_.device);
+    size_t kmax = opt_.max_span_chunks ? opt_.max_span_chunks : std::max<size_t>(1, (size_t)n_sm * 2 * 128 / (size_t)SC_);
     Kmax_ = (int)std::min<size_t>(kmax, 16384);
 
     if (!cfg.skip_processing && !opt_.stft_only && !opt_.forced_gains) {
@@ -165,6 +174,11 @@ Batch::~Batch() {
     if (stream_) cudaStreamSynchronize(stream_);
     if (scan_stream_) { cudaStreamSynchronize(scan_stream_); cudaStreamDestroy(scan_stream_); }
     if (scan_done_) cudaEventDestroy(scan_done_);
+    if (copy_stream_) { cudaStreamSynchronize(copy_stream_); cudaStreamDestroy(copy_stream_); }
+    for (int i = 0; i < 2; ++i) {
+        if (stage_ready_[i]) cudaEventDestroy(stage_ready_[i]);
+        if (stage_free_[i]) cudaEventDestroy(stage_free_[i]);
+    }
     tables_.release();
     for (auto &e : ev_) if (e) cudaEventDestroy(e);
     for (auto &sp : span_ev_) for (auto &e : sp) cudaEventDestroy(e);
@@ -309,22 +323,27 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
 }
 
 
-void Batch::push(const float *const *pcm, size_t n_pointers, size_t n, int memory) {
+// Ingest + run.  Host memory (and 16-bit PCM) goes through two stage buffers: the copy stream fills
+// buffer b with span i+1 while the compute stream runs span i out of buffer b^1, so H2D overlaps the
+// kernels.  Device f32 pointers with nothing pending are used in place.
+void Batch::push_any(const void *const *pcm, size_t n_pointers, size_t n, int memory, int fmt) {
     if (n_pointers != (size_t)SC_) throw Error(FVAD_ERR_CHANNEL_COUNT_MISMATCH, "expected n_streams*n_channels planar pointers");
     if (!pcm) throw Error(FVAD_ERR_INVALID_ARGUMENT, "pcm is NULL");
     for (int i = 0; i < SC_; ++i) {
         if (!pcm[i] && n) throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL channel pointer");
-        if (memory == 1 && (reinterpret_cast<uintptr_t>(pcm[i]) & 15)) throw Error(FVAD_ERR_INVALID_ARGUMENT, "device PCM pointers must be 16-byte aligned");
+        if (memory == 1 && fmt == 0 && (reinterpret_cast<uintptr_t>(pcm[i]) & 15)) throw Error(FVAD_ERR_INVALID_ARGUMENT, "device PCM pointers must be 16-byte aligned");
     }
     FVAD_CUDA_CHECK(cudaSetDevice(opt_.device));
     total_written_ += n;
     if (skip_ || n == 0) return;  // AudioPipeline.maybeRunPipeline: skip_processing (AudioPipeline.zig:211-214)
 
-    cudaStream_t s = stream_;
+    cudaStream_t s = stream_, cs = copy_stream_;
     const cudaMemcpyKind kind = memory == 1 ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const size_t esz = fmt ? sizeof(int16_t) : sizeof(float);
     const size_t total = (size_t)n_pend_ + n;
     const size_t Ktot = total / (size_t)chunk_;
     const size_t left = total % (size_t)chunk_;
+    auto src_at = [&](int i, size_t off) { return static_cast<const char *>(pcm[i]) + off * esz; };
 
     // taps cover exactly this push
     if (opt_.keep_taps) {
@@ -339,58 +358,85 @@ void Batch::push(const float *const *pcm, size_t n_pointers, size_t n, int memor
         taps_.ratio.ensure(std::max<size_t>((size_t)S_ * taps_.cap_vad, 1));
         taps_.met.ensure(std::max<size_t>((size_t)S_ * taps_.cap_vad, 1));
     }
+    if (fmt) pend_i16_.ensure((size_t)SC_ * chunk_);
 
     span_idx_ = 0;
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[6], s));
-    if (Ktot > 0) {
-        const bool zero_copy = (memory == 1 && n_pend_ == 0);
+    size_t src_off = 0;        // samples of the caller's buffers consumed by whole chunks
+    size_t pend_dst = 0;       // where the leftover goes inside pend_ rows
+    if (Ktot > 0 && memory == 1 && fmt == 0 && n_pend_ == 0) {
+        // ---- zero-copy: the caller's device buffers are the span input ----
         std::vector<const float *> hx((size_t)SC_);
-        if (zero_copy) {
-            for (int i = 0; i < SC_; ++i) hx[(size_t)i] = pcm[i];
-            FVAD_CUDA_CHECK(cudaMemcpyAsync(d_xptr_.p, hx.data(), hx.size() * sizeof(float *), cudaMemcpyHostToDevice, s));
-            FVAD_CUDA_CHECK(cudaStreamSynchronize(s));  // hx is a stack-lifetime pageable buffer
-            for (size_t k0 = 0; k0 < Ktot; k0 += (size_t)Kmax_) {
-                const int K = (int)std::min<size_t>((size_t)Kmax_, Ktot - k0);
-                process_span(d_xptr_.p, k0 * (size_t)chunk_, K);
-            }
-        } else {
-            // staged: [pending | new samples] per stream-channel, one span at a time
-            const size_t Kst = std::min<size_t>((size_t)Kmax_, Ktot);
-            const size_t spitch = Kst * (size_t)chunk_;
-            stage_.ensure((size_t)SC_ * spitch);
-            for (int i = 0; i < SC_; ++i) hx[(size_t)i] = stage_.p + (size_t)i * spitch;
-            FVAD_CUDA_CHECK(cudaMemcpyAsync(d_xptr_.p, hx.data(), hx.size() * sizeof(float *), cudaMemcpyHostToDevice, s));
-            FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
-            size_t src_off = 0;  // samples of the caller's buffers already consumed
-            for (size_t k0 = 0; k0 < Ktot; k0 += Kst) {
-                const size_t K = std::min<size_t>(Kst, Ktot - k0);
-                const size_t need = K * (size_t)chunk_;
-                const size_t from_pend = (k0 == 0) ? (size_t)n_pend_ : 0;
-                for (int i = 0; i < SC_; ++i) {
-                    float *dst = stage_.p + (size_t)i * spitch;
-                    if (from_pend)
-                        FVAD_CUDA_CHECK(cudaMemcpyAsync(dst, pend_.p + (size_t)i * chunk_, from_pend * sizeof(float), cudaMemcpyDeviceToDevice, s));
-                    FVAD_CUDA_CHECK(cudaMemcpyAsync(dst + from_pend, pcm[i] + src_off, (need - from_pend) * sizeof(float), kind, s));
-                }
-                src_off += need - from_pend;
-                process_span(d_xptr_.p, 0, (int)K);
-            }
-            // the remaining `left` samples start at src_off
-            for (int i = 0; i < SC_ && left; ++i)
-                FVAD_CUDA_CHECK(cudaMemcpyAsync(pend_.p + (size_t)i * chunk_, pcm[i] + src_off, left * sizeof(float), kind, s));
-            n_pend_ = (int)left;
-            goto done;
+        for (int i = 0; i < SC_; ++i) hx[(size_t)i] = static_cast<const float *>(pcm[i]);
+        FVAD_CUDA_CHECK(cudaMemcpyAsync(d_xptr_.p, hx.data(), hx.size() * sizeof(float *), cudaMemcpyHostToDevice, s));
+        FVAD_CUDA_CHECK(cudaStreamSynchronize(s));  // hx is a stack-lifetime pageable buffer
+        for (size_t k0 = 0; k0 < Ktot; k0 += (size_t)Kmax_) {
+            const int K = (int)std::min<size_t>((size_t)Kmax_, Ktot - k0);
+            process_span(d_xptr_.p, k0 * (size_t)chunk_, K);
         }
-        // zero-copy path: keep the tail that does not fill a chunk
-        for (int i = 0; i < SC_ && left; ++i)
-            FVAD_CUDA_CHECK(cudaMemcpyAsync(pend_.p + (size_t)i * chunk_, pcm[i] + Ktot * (size_t)chunk_, left * sizeof(float), kind, s));
-        n_pend_ = (int)left;
+        src_off = Ktot * (size_t)chunk_;
+    } else if (Ktot > 0) {
+        // ---- staged, double-buffered ----
+        const size_t Kst = std::min<size_t>((size_t)Kmax_, Ktot);
+        const size_t spitch = (Kst * (size_t)chunk_ + 7) & ~(size_t)7;
+        const int nbuf = Ktot > Kst ? 2 : 1;
+        bool moved = spitch != stage_pitch_;
+        for (int b = 0; b < nbuf; ++b) {
+            const float *old = stage_[b].p;
+            stage_[b].ensure((size_t)SC_ * spitch);
+            if (fmt) stage_i16_[b].ensure((size_t)SC_ * spitch);
+            moved = moved || old != stage_[b].p || !d_sptr_[b].p;
+        }
+        if (moved) {
+            stage_pitch_ = spitch;
+            std::vector<const float *> hx((size_t)SC_);
+            for (int b = 0; b < nbuf; ++b) {
+                d_sptr_[b].ensure((size_t)SC_);
+                for (int i = 0; i < SC_; ++i) hx[(size_t)i] = stage_[b].p + (size_t)i * spitch;
+                FVAD_CUDA_CHECK(cudaMemcpy(d_sptr_[b].p, hx.data(), hx.size() * sizeof(float *), cudaMemcpyHostToDevice));
+            }
+        } else if (nbuf == 2 && !d_sptr_[1].p) {
+            throw Error(FVAD_ERR_CUDA, "stage pointer table missing");
+        }
+        size_t span = 0;
+        for (size_t k0 = 0; k0 < Ktot; k0 += Kst, ++span) {
+            const int b = (int)(span & 1) % nbuf;
+            const size_t K = std::min<size_t>(Kst, Ktot - k0);
+            const size_t need = K * (size_t)chunk_;
+            const size_t from_pend = (k0 == 0) ? (size_t)n_pend_ : 0;
+            FVAD_CUDA_CHECK(cudaStreamWaitEvent(cs, stage_free_[b], 0));  // the span that last used buffer b is done
+            if (from_pend)
+                FVAD_CUDA_CHECK(cudaMemcpy2DAsync(stage_[b].p, spitch * sizeof(float), pend_.p, (size_t)chunk_ * sizeof(float),
+                                                  from_pend * sizeof(float), (size_t)SC_, cudaMemcpyDeviceToDevice, cs));
+            for (int i = 0; i < SC_; ++i) {
+                void *dst = fmt ? static_cast<void *>(stage_i16_[b].p + (size_t)i * spitch)
+                                : static_cast<void *>(stage_[b].p + (size_t)i * spitch + from_pend);
+                FVAD_CUDA_CHECK(cudaMemcpyAsync(dst, src_at(i, src_off), (need - from_pend) * esz, kind, cs));
+            }
+            src_off += need - from_pend;
+            FVAD_CUDA_CHECK(cudaEventRecord(stage_ready_[b], cs));
+            FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, stage_ready_[b], 0));
+            if (fmt) launch_i16_to_f32(stage_[b].p + from_pend, stage_i16_[b].p, spitch, spitch, need - from_pend, (size_t)SC_, s);
+            process_span(d_sptr_[b].p, 0, (int)K);
+            FVAD_CUDA_CHECK(cudaEventRecord(stage_free_[b], s));
+        }
     } else {
-        for (int i = 0; i < SC_; ++i)
-            FVAD_CUDA_CHECK(cudaMemcpyAsync(pend_.p + (size_t)i * chunk_ + n_pend_, pcm[i], n * sizeof(float), kind, s));
-        n_pend_ = (int)total;
+        pend_dst = (size_t)n_pend_;  // not a whole chunk yet: append
     }
-done:
+    // ---- the samples that do not fill a chunk wait in pend_ (VADPipeline.zig:150: never processed early) ----
+    const size_t n_left = Ktot > 0 ? left : n;
+    if (n_left) {
+        for (int i = 0; i < SC_; ++i) {
+            void *dst = fmt ? static_cast<void *>(pend_i16_.p + (size_t)i * chunk_)
+                            : static_cast<void *>(pend_.p + (size_t)i * chunk_ + pend_dst);
+            FVAD_CUDA_CHECK(cudaMemcpyAsync(dst, src_at(i, src_off), n_left * esz, kind, cs));
+        }
+    }
+    FVAD_CUDA_CHECK(cudaEventRecord(stage_ready_[0], cs));
+    FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, stage_ready_[0], 0));
+    if (n_left && fmt) launch_i16_to_f32(pend_.p + pend_dst, pend_i16_.p, (size_t)chunk_, (size_t)chunk_, n_left, (size_t)SC_, s);
+    n_pend_ = (int)left;
+
     FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));
     if (Ktot > 0 && !opt_.stft_only) fetch_segments();
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[7], s));

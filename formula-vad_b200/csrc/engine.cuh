@@ -27,7 +27,9 @@ public:
     ~Batch();
 
     // pcm: S*C planar pointers (stream-major), n samples each; memory 0 host / 1 device
-    void push(const float *const *pcm, size_t n_pointers, size_t n_samples, int memory);
+    void push(const float *const *pcm, size_t n_pointers, size_t n_samples, int memory) { push_any(reinterpret_cast<const void *const *>(pcm), n_pointers, n_samples, memory, 0); }
+    // same with 16-bit PCM (x / 32768, what libsndfile's sf_readf_float hands the reference: AudioFileStream.zig:56-102)
+    void push_i16(const int16_t *const *pcm, size_t n_pointers, size_t n_samples, int memory) { push_any(reinterpret_cast<const void *const *>(pcm), n_pointers, n_samples, memory, 1); }
     void segments(size_t stream, size_t machine, const fvad_segment **segs, size_t *n);
     size_t tap(int which, void *dst, size_t dst_bytes);
     void stats(fvad_batch_stats *out) const;
@@ -38,6 +40,7 @@ public:
     size_t chunk() const { return (size_t)chunk_; }
 
 private:
+    void push_any(const void *const *pcm, size_t n_pointers, size_t n_samples, int memory, int fmt);
     void process_span(const float *const *d_x, size_t x_offset, int K);
     void init_machines(const fvad_config &cfg);
     void fetch_segments();
@@ -46,8 +49,9 @@ private:
     size_t sample_rate_;
     fvad_batch_options opt_;
     int Kmax_;
-    cudaStream_t stream_ = nullptr, scan_stream_ = nullptr;
+    cudaStream_t stream_ = nullptr, scan_stream_ = nullptr, copy_stream_ = nullptr;
     cudaEvent_t scan_done_ = nullptr;
+    cudaEvent_t stage_ready_[2] = {}, stage_free_[2] = {};  // double-buffered ingest: copy stream <-> compute stream
     cudaEvent_t ev_[8] = {};
     std::vector<std::array<cudaEvent_t, 7>> span_ev_;  // per-span stage boundaries of the current push
     size_t span_idx_ = 0;
@@ -65,8 +69,10 @@ private:
     int parity_ = 0;               // which halo/tail carry buffer is current
 
     // device state
-    DevBuf<float> pend_, stage_;               // [SC][chunk], [SC][Kstage*chunk]
-    DevBuf<const float *> d_xptr_;             // [SC]
+    DevBuf<float> pend_, stage_[2];            // [SC][chunk], 2 x [SC][Kstage*chunk]
+    DevBuf<int16_t> pend_i16_, stage_i16_[2];             // raw 16-bit PCM of a span before conversion
+    DevBuf<const float *> d_xptr_, d_sptr_[2]; // [SC] caller's device pointers / stage buffer rows
+    size_t stage_pitch_ = 0;
     DevBuf<float> halo_[2], tail_[2];          // [SC][160]
     DevBuf<float> ctx_carry_, ylook_carry_, sumsq_carry_;
     DevBuf<fvad_complex> spec_;

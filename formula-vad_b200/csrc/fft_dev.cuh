@@ -119,6 +119,47 @@ __device__ __forceinline__ void warp_cfft(float2 (&v)[R], const float2 *__restri
     }
 }
 
+// Same transform with every lane-constant twiddle hoisted into registers (a kernel that runs many
+// frames per warp initialises this once).  The half-select of each butterfly is folded into the
+// operands: a = sg*v + b (sg = -1 in the upper half: b - v, +1 in the lower: v + b), then a * ws with
+// ws = (1, 0) in the lower half -- bit-identical to warp_cfft, ~40 % fewer instructions.
+template <int R, bool INV>
+struct WarpFftTw {
+    float2 t1[R > 1 ? R - 1 : 1];  // w_N^(lane*k1), k1 = 1..R-1
+    float2 ws[4];                  // stages h = 16, 8, 4, 2
+    float sg[5];                   // stages h = 16, 8, 4, 2, 1
+    __device__ __forceinline__ void init(const float2 *__restrict__ T, int lane) {
+        constexpr int N = 32 * R;
+#pragma unroll
+        for (int k1 = 1; k1 < R; ++k1) t1[k1 - 1] = tw<INV>(T[2 * lane * k1]);
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const int h = 16 >> i;
+            const bool upper = (lane & h) != 0;
+            sg[i] = upper ? -1.0f : 1.0f;
+            if (i < 4) ws[i] = upper ? tw<INV>(T[(lane & (h - 1)) * (N / h)]) : make_float2(1.0f, 0.0f);
+        }
+    }
+};
+
+template <int R, bool INV>
+__device__ __forceinline__ void warp_cfft_tw(float2 (&v)[R], const WarpFftTw<R, INV> &w) {
+    RegDft<R, INV>::run(v);
+#pragma unroll
+    for (int k1 = 1; k1 < R; ++k1) v[k1] = cmul(v[k1], w.t1[k1 - 1]);
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        const int h = 16 >> i;
+#pragma unroll
+        for (int k1 = 0; k1 < R; ++k1) {
+            float2 a;
+            a.x = fmaf(v[k1].x, w.sg[i], __shfl_xor_sync(0xffffffffu, v[k1].x, h));
+            a.y = fmaf(v[k1].y, w.sg[i], __shfl_xor_sync(0xffffffffu, v[k1].y, h));
+            v[k1] = i < 4 ? cmul(a, w.ws[i]) : a;  // the last stage's twiddle is 1 for every lane
+        }
+    }
+}
+
 // index of the value held by (lane, register k1) after warp_cfft
 template <int R>
 __device__ __forceinline__ int cfft_out_index(int lane, int k1) { return k1 + R * bitrev5(lane); }
@@ -136,6 +177,16 @@ __device__ __forceinline__ float2 rfft_bin(const float2 *__restrict__ Z, const f
     const float2 o = cmul(d, mi_t);
     // DC and Nyquist are purely real (kiss_fftr.c:82-89 writes their imaginary part as 0)
     return make_float2((e.x + o.x) * 0.5f, (k == 0 || k == N) ? 0.0f : (e.y + o.y) * 0.5f);
+}
+
+// The same unpack in kissfft's own pair form (kiss_fftr.c:93-116): bins k and N-k from Z[k], Z[N-k] and ONE
+// super twiddle st = exp(-i*pi*(k/N + 1/2)) = -i*T[k]; k in [1, N/2].
+__device__ __forceinline__ void rfft_pair(float2 zk, float2 znk, float2 st, float2 &Xk, float2 &Xnk) {
+    const float2 f1 = make_float2(zk.x + znk.x, zk.y - znk.y);
+    const float2 f2 = make_float2(zk.x - znk.x, zk.y + znk.y);
+    const float2 t = cmul(f2, st);
+    Xk = make_float2((f1.x + t.x) * 0.5f, (f1.y + t.y) * 0.5f);
+    Xnk = make_float2((f1.x - t.x) * 0.5f, (t.y - f1.y) * 0.5f);
 }
 
 // Inverse pre-pack (kiss_fftri, kiss_fftr.c:131-153): Zt[k] = (X[k]+conj(X[N-k])) + i*conj(T[k])*(X[k]-conj(X[N-k]))

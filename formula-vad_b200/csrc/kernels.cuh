@@ -95,5 +95,6 @@ void launch_vadscan(const ScanArgs &a, cudaStream_t s);
 
 // small helpers
 void launch_copy_rows(float *dst, const float *src, size_t dst_pitch, size_t src_pitch, size_t row_len, size_t rows, cudaStream_t s);
+void launch_i16_to_f32(float *dst, const int16_t *src, size_t dst_pitch, size_t src_pitch, size_t n, size_t rows, cudaStream_t s);
 
 }  // namespace fvad

@@ -83,32 +83,56 @@ __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const fl
     if (c == a.K - 1 && tid < kHop) a.halo_out[(size_t)sc * kHop + tid] = xs[kFrames * kHop + tid];
 
     // ---- frames ----
+    // lane-constant operands live in registers for all five frames of this warp
+    WarpFftTw<5, false> ftw;
+    ftw.init(T, lane);
+    float2 wreg[5], st[3];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) wreg[q] = *reinterpret_cast<const float2 *>(win + 2 * (lane + 32 * q));
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const float2 t = T[(lane + 32 * q) & 255];  // pairs k = lane + 32q <= 80 are used
+        st[q] = make_float2(t.y, -t.x);             // super twiddle -i*T[k] (kiss_fftr.c:104)
+    }
     float2 *Z = zb[warp];
     for (int f = warp; f < kFrames; f += kStftWarps) {
         const float *fx = xs + f * kHop;
         float2 v[5];
 #pragma unroll
         for (int q = 0; q < 5; ++q) {
-            const int n = lane + 32 * q;
-            const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * n);
-            const float2 w2 = *reinterpret_cast<const float2 *>(win + 2 * n);
-            v[q] = make_float2(s2.x * w2.x, s2.y * w2.y);  // FFT.zig:188-196 window multiply
+            const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * (lane + 32 * q));
+            v[q] = make_float2(s2.x * wreg[q].x, s2.y * wreg[q].y);  // FFT.zig:188-196 window multiply
         }
-        warp_cfft<5, false>(v, T, lane);
+        warp_cfft_tw<5, false>(v, ftw);
 #pragma unroll
         for (int k1 = 0; k1 < 5; ++k1) Z[cfft_out_index<5>(lane, k1)] = v[k1];
         __syncwarp();
         const size_t row = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames + f;
         const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
+        float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
+        float *frw = a.feat + frow * kBins;
+        // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no FMA);
+        // the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, far inside every parity gate)
+        auto emit = [&](int k, float2 X) {
+            if (srow) srow[k] = X;
+            const float pw = __fadd_rn(__fmul_rn(X.x, X.x), __fmul_rn(X.y, X.y));
+            frw[k] = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
+        };
+        // real-FFT unpack in kissfft's pair form: lane handles bins k and 160-k, k = lane + 32q in [0, 80]
 #pragma unroll
-        for (int q = 0; q < 6; ++q) {
+        for (int q = 0; q < 3; ++q) {
             const int k = lane + 32 * q;
-            if (k <= kHop) {
-                const float2 X = rfft_bin(Z, T, kHop, k);
-                if (a.spec) reinterpret_cast<float2 *>(a.spec)[row * kBins + k] = X;
-                // NSNet2.zig:275-284 (no FMA contraction: pow(r,2)+pow(i,2) then max, log10)
-                const float pw = __fadd_rn(__fmul_rn(X.x, X.x), __fmul_rn(X.y, X.y));
-                a.feat[frow * kBins + k] = log10f(fmaxf(pw, 1e-12f));
+            if (k <= kHop / 2) {
+                const float2 zk = Z[k];
+                if (k == 0) {  // DC and Nyquist (kiss_fftr.c:82-89)
+                    emit(0, make_float2(zk.x + zk.y, 0.0f));
+                    emit(kHop, make_float2(zk.x - zk.y, 0.0f));
+                } else {
+                    float2 Xk, Xnk;
+                    rfft_pair(zk, Z[kHop - k], st[q], Xk, Xnk);
+                    if (k != kHop - k) emit(k, Xk);  // at k = 80 kissfft's second store wins
+                    emit(kHop - k, Xnk);
+                }
             }
         }
         __syncwarp();

@@ -88,4 +88,42 @@ void launch_copy_rows(float *dst, const float *src, size_t dst_pitch, size_t src
     FVAD_LAUNCHED();
 }
 
+// 16-bit PCM -> f32, x * 2^-15 (libsndfile's normalised float read, the reference's ingest:
+// src/audio_utils/AudioFileStream.zig:56-102).  rows x n elements, 8 samples per thread.
+__global__ void i16_to_f32_kernel(float *dst, const int16_t *src, size_t dst_pitch, size_t src_pitch, size_t n, size_t rows) {
+    const size_t n8 = n / 8, per_row = n8 + 1;  // the last slot of a row handles the n % 8 tail
+    const size_t total = per_row * rows;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / per_row, c = i % per_row;
+        const int16_t *sp = src + r * src_pitch;
+        float *dp = dst + r * dst_pitch;
+        const bool vec = ((reinterpret_cast<uintptr_t>(sp) | reinterpret_cast<uintptr_t>(dp)) & 15) == 0;
+        if (c < n8 && vec) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(sp + c * 8);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                o[2 * k] = (float)(int16_t)(w[k] & 0xFFFFu) * (1.0f / 32768.0f);
+                o[2 * k + 1] = (float)(int16_t)(w[k] >> 16) * (1.0f / 32768.0f);
+            }
+            *reinterpret_cast<float4 *>(dp + c * 8) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float4 *>(dp + c * 8 + 4) = make_float4(o[4], o[5], o[6], o[7]);
+        } else if (c < n8) {
+            for (size_t k = c * 8; k < c * 8 + 8; ++k) dp[k] = (float)sp[k] * (1.0f / 32768.0f);
+        } else {
+            for (size_t k = n8 * 8; k < n; ++k) dp[k] = (float)sp[k] * (1.0f / 32768.0f);
+        }
+    }
+}
+
+// pitches must be multiples of 8 elements and the bases 16-byte aligned (stage buffers are)
+void launch_i16_to_f32(float *dst, const int16_t *src, size_t dst_pitch, size_t src_pitch, size_t n, size_t rows, cudaStream_t s) {
+    if (!rows || !n) return;
+    const size_t total = (n / 8 + 1) * rows;
+    const int grid = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
+    i16_to_f32_kernel<<<grid, 256, 0, s>>>(dst, src, dst_pitch, src_pitch, n, rows);
+    FVAD_LAUNCHED();
+}
+
 }  // namespace fvad

@@ -255,10 +255,17 @@ class BatchPipeline:
         ptrs = (C.c_void_p * pcm.shape[0])(*[pcm[i].ctypes.data for i in range(pcm.shape[0])])
         check(self._L.fvad_batch_push(self._h, ptrs, pcm.shape[0], pcm.shape[1], 0))
 
-    def push_pointers(self, pointers, n_samples: int, on_device: bool):
+    def push_i16(self, pcm: np.ndarray):
+        """pcm: host int16 [n_streams*n_channels, n]; converted on the device as x / 32768."""
+        pcm = np.ascontiguousarray(pcm, np.int16)
+        ptrs = (C.c_void_p * pcm.shape[0])(*[pcm[i].ctypes.data for i in range(pcm.shape[0])])
+        check(self._L.fvad_batch_push_i16(self._h, ptrs, pcm.shape[0], pcm.shape[1], 0))
+
+    def push_pointers(self, pointers, n_samples: int, on_device: bool, i16: bool = False):
         """pointers: ints (host or device addresses), one per stream-channel."""
         ptrs = (C.c_void_p * len(pointers))(*pointers)
-        check(self._L.fvad_batch_push(self._h, ptrs, len(pointers), n_samples, 1 if on_device else 0))
+        fn = self._L.fvad_batch_push_i16 if i16 else self._L.fvad_batch_push
+        check(fn(self._h, ptrs, len(pointers), n_samples, 1 if on_device else 0))
 
     def segments(self, stream: int, machine: int = 0):
         p, n = C.POINTER(capi.Segment)(), C.c_size_t()
@@ -272,6 +279,8 @@ class BatchPipeline:
         out = np.empty(n.value, dt)
         check(self._L.fvad_batch_tap(self._h, which, out.ctypes.data, out.nbytes, C.byref(n)))
         sc = self.n_streams * self.n_channels
+        if out.size == 0:
+            return out.reshape((sc, 0, 161) if which in (capi.TAP_SPECTRUM, capi.TAP_FEATURES, capi.TAP_GAINS) else (sc, 0))
         if which in (capi.TAP_SPECTRUM, capi.TAP_FEATURES, capi.TAP_GAINS):
             return out.reshape(sc, -1, 161)
         if which in (capi.TAP_DENOISED16, capi.TAP_DENOISED):

@@ -52,6 +52,11 @@ def onboard_stream(seed: int, seconds: float, sample_rate: int = 16000, n_channe
     return np.stack(chans), labels
 
 
+def pcm16(x: np.ndarray) -> np.ndarray:
+    """float [-1, 1) -> int16 the way a 16-bit WAV stores it (round to nearest, clipped)."""
+    return np.clip(np.rint(np.asarray(x, np.float64) * 32768.0), -32768, 32767).astype(np.int16)
+
+
 def expand_16k_to_48k(x16: np.ndarray) -> np.ndarray:
     """x48[3i] = x16[i], the two samples in between linearly interpolated: the
     reference's decimate-by-3 then recovers x16 exactly."""

@@ -200,9 +200,16 @@ FVAD_API int fvad_batch_create(size_t n_streams, const fvad_config *cfg, const f
                                const fvad_batch_options *opt, fvad_batch **out);
 FVAD_API void fvad_batch_destroy(fvad_batch *b);
 /* pcm: n_streams*n_channels planar pointers (stream-major), n_samples each.  memory: 0 host,
- * 1 device (16-byte aligned).  Every complete chunk of every stream is processed. */
+ * 1 device (16-byte aligned).  Every complete chunk of every stream is processed.  Host memory is
+ * ingested through two device stage buffers so the copy of span i+1 overlaps the kernels of span i
+ * (pinned host memory makes the copy asynchronous). */
 FVAD_API int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n_pointers, size_t n_samples,
                              int memory);
+/* same with 16-bit PCM, converted on the device as x / 32768 -- the normalisation libsndfile applies when the
+ * reference reads its WAV input as float (src/audio_utils/AudioFileStream.zig:56-102,
+ * simulator/SimulationInstance.zig:183-213); halves the host->device bytes. */
+FVAD_API int fvad_batch_push_i16(fvad_batch *b, const int16_t *const *pcm, size_t n_pointers, size_t n_samples,
+                                 int memory);
 FVAD_API int fvad_batch_segments(fvad_batch *b, size_t stream, size_t machine, const fvad_segment **segments,
                                  size_t *n);
 /* sizes are returned in elements of the tap's type for the LAST push; dst may be NULL to query */

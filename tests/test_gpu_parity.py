@@ -113,7 +113,7 @@ def test_full_pipeline_parity_single_push(fv, po, wd, sr, nch):
     g_met = gp.tap(fv.capi.TAP_MET)[0]
     assert g_band.shape == band.shape and len(band) == (x.shape[1] // (8000 * sr // 16000)) * (8000 * sr // 16000) // 1024
     assert np.abs(g_band - band).max() < 2e-4 * np.abs(band).max()
-    assert np.abs(g_ratio - ratio).max() < 1e-5
+    assert np.abs(g_ratio - ratio).max() < 5e-5  # sequential-f32-sum rounding of the reference, see below
     assert (g_met == met).mean() >= 0.999
     assert _segments_close(gp.segments(0), op.segments(0), 1024)
 
@@ -141,8 +141,8 @@ def test_dsp_parity_with_forced_gains_is_tight(fv, po, wd):
     band, ratio, met = op.frames()
     assert np.abs(gp.tap(fv.capi.TAP_BAND)[0] - band).max() < 5e-6 * np.abs(band).max()
     # the reference sums 24 000 squares sequentially in f32 (audio_utils.zig:14-24); the GPU tree-reduces, so
-    # the chunk RMS differs by f32 summation-order rounding (~1e-6 relative)
-    assert np.abs(gp.tap(fv.capi.TAP_RATIO)[0] - ratio).max() < 1e-5
+    # the chunk RMS differs by f32 summation-order rounding (the sequential sum itself is off by ~sqrt(n)*2^-24 ~ 1e-5)
+    assert np.abs(gp.tap(fv.capi.TAP_RATIO)[0] - ratio).max() < 5e-5
     assert (gp.tap(fv.capi.TAP_MET)[0] == met).all()
     assert gp.segments(0) == op.segments(0) or _segments_close(gp.segments(0), op.segments(0), 0)
 
@@ -227,3 +227,31 @@ def test_nsnet2_operator_and_pipeline_facade(fv, po, wd):
         p.push_samples([x[:10]])
     assert e.value.name == "ChannelCountMismatch"
     assert p.vad_segments() == []
+
+
+def test_double_buffered_host_ingest_and_int16(fv, wd):
+    """Host pushes run through two stage buffers (copy of span i+1 overlaps span i); 16-bit PCM is converted
+    on the device as x/32768.  Both must reproduce, bit for bit, the single-span run on the same samples."""
+    sr, S = 16000, 2
+    x16 = np.stack([fv.synth.pcm16(fv.synth.onboard_stream(40 + s, 33.3, sr, 1)[0][0]) for s in range(S)])
+    x = x16.astype(np.float32) / np.float32(32768.0)
+    ref = fv.BatchPipeline(S, sr, 1, wd, keep_taps=True)          # one span
+    ref.push(x)
+    r_band, r_gain = ref.tap(fv.capi.TAP_BAND), ref.tap(fv.capi.TAP_GAINS)
+    r_segs = [ref.segments(s) for s in range(S)]
+    ref.close()
+    assert any(len(s) for s in r_segs)
+    for i16 in (False, True):
+        for cuts in ([0, x.shape[1]], [0, 5, 12345, 200001, 200002, x.shape[1]]):
+            gp = fv.BatchPipeline(S, sr, 1, wd, keep_taps=True, max_span_chunks=3)  # many spans, both buffers
+            bands, gains = [], []
+            for a, b in zip(cuts[:-1], cuts[1:]):
+                gp.push_i16(x16[:, a:b]) if i16 else gp.push(x[:, a:b])
+                if gp.tap(fv.capi.TAP_BAND).size:
+                    bands.append(gp.tap(fv.capi.TAP_BAND))
+                if gp.tap(fv.capi.TAP_GAINS).size:
+                    gains.append(gp.tap(fv.capi.TAP_GAINS))
+            assert np.array_equal(np.concatenate(bands, axis=1), r_band), (i16, cuts)
+            assert np.array_equal(np.concatenate(gains, axis=1), r_gain), (i16, cuts)
+            assert [gp.segments(s) for s in range(S)] == r_segs
+            gp.close()
