@@ -32,6 +32,17 @@ __global__ void __launch_bounds__(kIstftThreads) istft_kernel(IstftArgs a, const
     const float *__restrict__ wn = gwn;  // 1.25 KB, L1-resident; keeps static shared memory under 48 KB
     __syncthreads();
 
+    // lane-constant operands in registers for all frames of this warp: FFT twiddles, the pre-pack
+    // twiddles i*conj(T[k]) and the synthesis window (window*1/320) at this lane's output positions
+    WarpFftTw<5, true> ftw;
+    ftw.init(T, lane);
+    float2 itw[5], wreg[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+        const float2 t = T[lane + 32 * q];
+        itw[q] = make_float2(t.y, t.x);
+        wreg[q] = __ldg(reinterpret_cast<const float2 *>(wn) + cfft_out_index<5>(lane, q));
+    }
     float2 *X = xb[warp];
     const size_t row0 = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames;  // row of chunk frame 0
     for (int pass = 0; pass < 2; ++pass) {
@@ -61,21 +72,25 @@ __global__ void __launch_bounds__(kIstftThreads) istft_kernel(IstftArgs a, const
             __syncwarp();
             float2 v[5];
 #pragma unroll
-            for (int q = 0; q < 5; ++q) v[q] = irfft_pack(X, T, kHop, lane + 32 * q);
-            warp_cfft<5, true>(v, T, lane);
+            for (int q = 0; q < 5; ++q) {  // kiss_fftri pre-pack (kiss_fftr.c:131-153)
+                const int k = lane + 32 * q;
+                const float2 xa = X[k], xb2 = X[kHop - k];
+                const float2 e = make_float2(xa.x + xb2.x, xa.y - xb2.y), d = make_float2(xa.x - xb2.x, xa.y + xb2.y);
+                v[q] = cadd(e, cmul(d, itw[q]));
+            }
+            warp_cfft_tw<5, true>(v, ftw);
 #pragma unroll
             for (int k1 = 0; k1 < 5; ++k1) {
                 const int n = cfft_out_index<5>(lane, k1);
                 // NSNet2.zig:335-336: inv *= window*norm; out += inv
-                const float2 w2 = __ldg(reinterpret_cast<const float2 *>(wn) + n);
-                const float r0 = v[k1].x * w2.x, r1 = v[k1].y * w2.y;
-                if (pass == 0) {
-                    yo[2 * n] = r0;
-                    yo[2 * n + 1] = r1;
-                } else {
-                    yo[2 * n] += r0;
-                    yo[2 * n + 1] += r1;
+                float2 r = make_float2(v[k1].x * wreg[k1].x, v[k1].y * wreg[k1].y);
+                float2 *dst = reinterpret_cast<float2 *>(yo) + n;
+                if (pass == 1) {
+                    const float2 o = *dst;
+                    r.x += o.x;
+                    r.y += o.y;
                 }
+                *dst = r;
             }
             __syncwarp();
         }

@@ -7,22 +7,170 @@
 //   NSNet2.calcFeatures           (NSNet2.zig:266-287) log10(max(re^2+im^2, 1e-12))
 //   audio_utils.rmsVolume         (audio_utils.zig:14-24) -- only the sum of squares here
 //
-// One CTA per (chunk, stream-channel): the chunk's D*8000 input samples are read from HBM exactly
-// once with 128-bit loads, squared-and-summed, decimated into shared memory (51 hops = 160-sample
-// halo + 8000), then ten warps run five 320-point frames each through the register/shuffle FFT.
+// A CTA works on one chunk at a time: the chunk's D*8000 input samples are read from HBM exactly
+// once, squared-and-summed, decimated into shared memory (51 hops = 160-sample halo + 8000), then ten
+// warps run five 320-point frames each through the register/shuffle FFT.  At D = 1 (16 kHz input) a
+// CTA walks kChunksPerCta consecutive chunks and one elected thread prefetches the next chunk into
+// the other half of a double-buffered tile with cp.async.bulk + mbarrier while the warps transform
+// the current one, so no warp ever waits on HBM; at D = 3 the decimating loads are batched.
 // Algorithmic HBM bytes per frame: 160*D*4 read + 161*4 features (+ 161*8 spectrum) written.
 #include "fft_dev.cuh"
 #include "kernels.cuh"
+#include "tc_dev.cuh"
 
 namespace fvad {
 
 constexpr int kStftThreads = 320;
 constexpr int kStftWarps = kStftThreads / 32;
+constexpr int kXs = (kFrames + 1) * kHop;  // decimated tile: halo hop + 50 hops
+constexpr int kChunksPerCta = 8;
 
+// lane-constant operands of the frame transform, held in registers across frames
+struct StftLaneConst {
+    WarpFftTw<5, false> ftw;
+    float2 wreg[5], st[3];
+    __device__ __forceinline__ void init(const float2 *__restrict__ T, const float *__restrict__ win, int lane) {
+        ftw.init(T, lane);
+#pragma unroll
+        for (int q = 0; q < 5; ++q) wreg[q] = *reinterpret_cast<const float2 *>(win + 2 * (lane + 32 * q));
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const float2 t = T[(lane + 32 * q) & 255];  // pairs k = lane + 32q <= 80 are used
+            st[q] = make_float2(t.y, -t.x);             // super twiddle -i*T[k] (kiss_fftr.c:104)
+        }
+    }
+};
+
+// frames f = warp, warp+10, ... of the tile xs -> spectrum rows / feature rows
+__device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneConst &lc, const float *__restrict__ xs,
+                                            float2 *__restrict__ Z, int sc, int c, int warp, int lane) {
+    for (int f = warp; f < kFrames; f += kStftWarps) {
+        const float *fx = xs + f * kHop;
+        float2 v[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * (lane + 32 * q));
+            v[q] = make_float2(s2.x * lc.wreg[q].x, s2.y * lc.wreg[q].y);  // FFT.zig:188-196 window multiply
+        }
+        warp_cfft_tw<5, false>(v, lc.ftw);
+#pragma unroll
+        for (int k1 = 0; k1 < 5; ++k1) Z[cfft_out_index<5>(lane, k1)] = v[k1];
+        __syncwarp();
+        const size_t row = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames + f;
+        const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
+        float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
+        float *frw = a.feat + frow * kBins;
+        // real-FFT unpack in kissfft's pair form (kiss_fftr.c:93-116): the lane handles bins k and 160-k for
+        // k = lane + 32q in [0, 80].  k = 0 runs through the same arithmetic with Z[0] as its own partner
+        // (gives DC = x + y, Nyquist = x - y, imaginary parts 0, kiss_fftr.c:82-89); at k = 80 both stores hit
+        // bin 80 and the second wins, as in kissfft.
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const int k = lane + 32 * q;
+            if (q < 2 || k <= kHop / 2) {
+                float2 X[2];
+                rfft_pair(Z[k], Z[k ? kHop - k : 0], lc.st[q], X[0], X[1]);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int kk = h ? kHop - k : k;
+                    if (srow) srow[kk] = X[h];
+                    // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no
+                    // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate)
+                    const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
+                    frw[kk] = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// block-wide sum of the per-thread partial sums of squares -> sumsq slot of chunk c (thread 0 writes)
+__device__ __forceinline__ void stft_sumsq(const StftArgs &a, float ss, float *red, int sc, int c, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (lane == 0) red[warp] = ss;
+    __syncthreads();
+    if (tid == 0) {
+        float t = 0.0f;
+#pragma unroll
+        for (int w = 0; w < kStftWarps; ++w) t += red[w];
+        a.sumsq[(size_t)sc * (a.K + 1) + 1 + c] = t;  // slot 0 of each row = last chunk of the previous span
+    }
+}
+
+// ---- D = 1: persistent over kChunksPerCta chunks, double-buffered bulk prefetch ----
+struct StftSmem1 {
+    float xs[2][kXs];          // 2 x 32 640 B
+    float2 T[256];
+    float win[kNfft];
+    float2 zb[kStftWarps][kHop];
+    float red[kStftWarps];
+    uint64_t full[2];
+};
+
+__global__ void __launch_bounds__(kStftThreads, 2) stft_kernel_d1(StftArgs a, const float2 *__restrict__ gT,
+                                                                  const float *__restrict__ gwin) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    StftSmem1 &sm = *reinterpret_cast<StftSmem1 *>(smem_raw);
+    const int sc = blockIdx.y;
+    const int c_begin = blockIdx.x * kChunksPerCta, c_end = min(a.K, c_begin + kChunksPerCta);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *__restrict__ xrow = a.x[sc] + a.x_offset;
+
+    // chunk c -> buffer b: the 160 samples before the chunk are its halo (for the span's first chunk they come
+    // from the carry buffer instead and only the 8000 new samples are fetched)
+    auto prefetch = [&](int c, int b) {
+        const float *src = xrow + (size_t)c * kChunk16 - (c ? kHop : 0);
+        float *dst = sm.xs[b] + (c ? 0 : kHop);
+        const uint32_t bytes = (uint32_t)((c ? kXs : kChunk16) * sizeof(float));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic accesses to this buffer are ordered first
+        tc::mbar_expect_tx(&sm.full[b], bytes);
+        tc::bulk_g2s(dst, src, bytes, &sm.full[b]);
+    };
+    if (tid == 0) {
+        tc::mbar_init(&sm.full[0], 1);
+        tc::mbar_init(&sm.full[1], 1);
+        tc::fence_mbar_init();
+        prefetch(c_begin, 0);
+    }
+    for (int i = tid; i < kNfft; i += kStftThreads) {
+        if (i < 256) sm.T[i] = gT[i];
+        sm.win[i] = gwin[i];
+    }
+    __syncthreads();
+    StftLaneConst lc;
+    lc.init(sm.T, sm.win, lane);
+
+    for (int c = c_begin, it = 0; c < c_end; ++c, ++it) {
+        const int b = it & 1;
+        // the other buffer was last read in the previous iteration, which ended with __syncthreads
+        if (tid == 0 && c + 1 < c_end) prefetch(c + 1, b ^ 1);
+        tc::mbar_wait(&sm.full[b], (it >> 1) & 1);
+        float *xs = sm.xs[b];
+        if (c == 0 && tid < kHop) xs[tid] = a.halo_in[(size_t)sc * kHop + tid];
+        // sum of squares of the chunk's own 8000 samples (same per-thread order as a strided 128-bit global read)
+        float ss = 0.0f;
+        for (int i = tid; i < kChunk16 / 4; i += kStftThreads) {
+            const float4 v = *reinterpret_cast<const float4 *>(&xs[kHop + 4 * i]);
+            ss = fmaf(v.x, v.x, ss);
+            ss = fmaf(v.y, v.y, ss);
+            ss = fmaf(v.z, v.z, ss);
+            ss = fmaf(v.w, v.w, ss);
+        }
+        stft_sumsq(a, ss, sm.red, sc, c, tid);  // contains a __syncthreads: the halo rows are visible after it
+        if (c == a.K - 1 && tid < kHop) a.halo_out[(size_t)sc * kHop + tid] = xs[kFrames * kHop + tid];
+        stft_frames(a, lc, xs, sm.zb[warp], sc, c, warp, lane);
+        __syncthreads();
+    }
+}
+
+// ---- general D (48 kHz input: D = 3): one chunk per CTA, decimating loads ----
 template <int D>
 __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const float2 *__restrict__ gT,
                                                             const float *__restrict__ gwin) {
-    __shared__ __align__(16) float xs[(kFrames + 1) * kHop];  // decimated: halo hop + 50 hops
+    __shared__ __align__(16) float xs[kXs];
     __shared__ float2 T[256];  // indices used by the N=160 transform stay below 249
     __shared__ float win[kNfft];
     __shared__ float2 zb[kStftWarps][kHop];
@@ -43,18 +191,25 @@ __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const fl
     {
         const float4 *x4 = reinterpret_cast<const float4 *>(x);
         constexpr int n4 = kChunk16 * D / 4;
-        for (int i = tid; i < n4; i += kStftThreads) {
-            const float4 v = __ldg(x4 + i);
-            ss = fmaf(v.x, v.x, ss);
-            ss = fmaf(v.y, v.y, ss);
-            ss = fmaf(v.z, v.z, ss);
-            ss = fmaf(v.w, v.w, ss);
-            if (D == 1) {
-                *reinterpret_cast<float4 *>(&xs[kHop + 4 * i]) = v;
-            } else {
+        constexpr int kBatch = 5;  // loads in flight per thread
+        for (int i0 = tid; i0 < n4; i0 += kStftThreads * kBatch) {
+            float4 v[kBatch];
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) {
+                const int i = i0 + u * kStftThreads;
+                v[u] = i < n4 ? __ldg(x4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) {
+                const int i = i0 + u * kStftThreads;
+                if (i >= n4) break;
+                ss = fmaf(v[u].x, v[u].x, ss);
+                ss = fmaf(v[u].y, v[u].y, ss);
+                ss = fmaf(v[u].z, v[u].z, ss);
+                ss = fmaf(v[u].w, v[u].w, ss);
                 // sample index s = 4i+j is kept when s % D == 0, at xs[hop + s/D]
                 const int s0 = 4 * i;
-                const float e[4] = {v.x, v.y, v.z, v.w};
+                const float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     if ((s0 + j) % D == 0) xs[kHop + (s0 + j) / D] = e[j];
@@ -62,89 +217,32 @@ __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const fl
         }
     }
     // halo: the 160 decimated samples that precede this chunk
-    if (tid < kHop) {
-        float h;
-        if (c == 0) h = a.halo_in[(size_t)sc * kHop + tid];
-        else h = __ldg(x - (size_t)(kHop - tid) * D);
-        xs[tid] = h;
-    }
-    // block reduction of the sum of squares
-#pragma unroll
-    for (int o = 16; o; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    if (lane == 0) red[warp] = ss;
-    __syncthreads();
-    if (tid == 0) {
-        float t = 0.0f;
-#pragma unroll
-        for (int w = 0; w < kStftWarps; ++w) t += red[w];
-        a.sumsq[(size_t)sc * (a.K + 1) + 1 + c] = t;  // slot 0 of each row = last chunk of the previous span
-    }
+    if (tid < kHop) xs[tid] = (c == 0) ? a.halo_in[(size_t)sc * kHop + tid] : __ldg(x - (size_t)(kHop - tid) * D);
+    stft_sumsq(a, ss, red, sc, c, tid);
     // the last chunk of the span leaves its last hop as the next span's halo
     if (c == a.K - 1 && tid < kHop) a.halo_out[(size_t)sc * kHop + tid] = xs[kFrames * kHop + tid];
 
-    // ---- frames ----
-    // lane-constant operands live in registers for all five frames of this warp
-    WarpFftTw<5, false> ftw;
-    ftw.init(T, lane);
-    float2 wreg[5], st[3];
-#pragma unroll
-    for (int q = 0; q < 5; ++q) wreg[q] = *reinterpret_cast<const float2 *>(win + 2 * (lane + 32 * q));
-#pragma unroll
-    for (int q = 0; q < 3; ++q) {
-        const float2 t = T[(lane + 32 * q) & 255];  // pairs k = lane + 32q <= 80 are used
-        st[q] = make_float2(t.y, -t.x);             // super twiddle -i*T[k] (kiss_fftr.c:104)
-    }
-    float2 *Z = zb[warp];
-    for (int f = warp; f < kFrames; f += kStftWarps) {
-        const float *fx = xs + f * kHop;
-        float2 v[5];
-#pragma unroll
-        for (int q = 0; q < 5; ++q) {
-            const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * (lane + 32 * q));
-            v[q] = make_float2(s2.x * wreg[q].x, s2.y * wreg[q].y);  // FFT.zig:188-196 window multiply
-        }
-        warp_cfft_tw<5, false>(v, ftw);
-#pragma unroll
-        for (int k1 = 0; k1 < 5; ++k1) Z[cfft_out_index<5>(lane, k1)] = v[k1];
-        __syncwarp();
-        const size_t row = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames + f;
-        const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
-        float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
-        float *frw = a.feat + frow * kBins;
-        // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no FMA);
-        // the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, far inside every parity gate)
-        auto emit = [&](int k, float2 X) {
-            if (srow) srow[k] = X;
-            const float pw = __fadd_rn(__fmul_rn(X.x, X.x), __fmul_rn(X.y, X.y));
-            frw[k] = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
-        };
-        // real-FFT unpack in kissfft's pair form: lane handles bins k and 160-k, k = lane + 32q in [0, 80]
-#pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            const int k = lane + 32 * q;
-            if (k <= kHop / 2) {
-                const float2 zk = Z[k];
-                if (k == 0) {  // DC and Nyquist (kiss_fftr.c:82-89)
-                    emit(0, make_float2(zk.x + zk.y, 0.0f));
-                    emit(kHop, make_float2(zk.x - zk.y, 0.0f));
-                } else {
-                    float2 Xk, Xnk;
-                    rfft_pair(zk, Z[kHop - k], st[q], Xk, Xnk);
-                    if (k != kHop - k) emit(k, Xk);  // at k = 80 kissfft's second store wins
-                    emit(kHop - k, Xnk);
-                }
-            }
-        }
-        __syncwarp();
-    }
+    StftLaneConst lc;
+    lc.init(T, win, lane);
+    stft_frames(a, lc, xs, zb[warp], sc, c, warp, lane);
 }
 
 void launch_stft(const StftArgs &a, const Tables &t, cudaStream_t s) {
     if (a.K <= 0 || a.SC <= 0) return;
-    dim3 grid((unsigned)a.K, (unsigned)a.SC);
-    if (a.D == 1) stft_kernel<1><<<grid, kStftThreads, 0, s>>>(a, t.T320, t.win320);
-    else if (a.D == 3) stft_kernel<3><<<grid, kStftThreads, 0, s>>>(a, t.T320, t.win320);
-    else throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "unsupported decimation factor");
+    if (a.D == 1) {
+        static bool attr = false;
+        if (!attr) {
+            FVAD_CUDA_CHECK(cudaFuncSetAttribute(stft_kernel_d1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StftSmem1)));
+            attr = true;
+        }
+        dim3 grid((unsigned)((a.K + kChunksPerCta - 1) / kChunksPerCta), (unsigned)a.SC);
+        stft_kernel_d1<<<grid, kStftThreads, sizeof(StftSmem1), s>>>(a, t.T320, t.win320);
+    } else if (a.D == 3) {
+        dim3 grid((unsigned)a.K, (unsigned)a.SC);
+        stft_kernel<3><<<grid, kStftThreads, 0, s>>>(a, t.T320, t.win320);
+    } else {
+        throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "unsupported decimation factor");
+    }
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
 }

@@ -12,12 +12,14 @@
 //   VADMetadata weighted merge            (VADMetadata.zig:29-60) through the three buffered steps
 //
 // One CTA per (VAD frame, stream); warp w handles channel w (channels beyond the warp count loop).
+#include <algorithm>
+
 #include "fft_dev.cuh"
 #include "kernels.cuh"
 
 namespace fvad {
 
-constexpr int kVadWarps = 2;
+constexpr int kVadWarps = 8;
 constexpr int kVadThreads = 32 * kVadWarps;
 constexpr int kMaxBands = 8;
 
@@ -38,113 +40,123 @@ __device__ __forceinline__ float chunk_ratio(const float *__restrict__ sumsq, in
     return r;
 }
 
-template <int D>
-__global__ void __launch_bounds__(kVadThreads) vadfft_kernel(VadFftArgs a, const float2 *__restrict__ gT,
-                                                             const float *__restrict__ ghann, float norm) {
-    __shared__ float2 T[1024];
-    __shared__ float2 zb[kVadWarps][512];
-    __shared__ float chband[kVadWarps][kMaxBands];
+// One warp per (VAD frame, stream) item, eight warps per CTA, CTAs loop over items: the 8 KB twiddle
+// table is staged once per CTA and every lane-constant operand (FFT twiddles, Hann weights) sits in
+// registers across items.  The band sum is a per-lane partial + xor reduction (the reference sums the
+// 33 bins sequentially, BufferedFFT.zig:190-199; the difference is f32 summation order, ~1e-7 relative,
+// below the FFT's own rounding distance to kissfft).
+// rfft_bin over the padded Z (element k lives at k + k/16)
+__device__ __forceinline__ float2 rfft_bin_padded(const float2 *__restrict__ Z, const float2 *__restrict__ T, int N, int k) {
+    const int ia = (k == N) ? 0 : k, ib = (k == 0) ? 0 : N - k;
+    const float2 a = Z[ia + (ia >> 4)];
+    const float2 bb = Z[ib + (ib >> 4)];
+    const float2 b = make_float2(bb.x, -bb.y);
+    const float2 e = cadd(a, b), d = csub(a, b);
+    const float2 t = T[k];
+    const float2 o = cmul(d, make_float2(t.y, -t.x));
+    return make_float2((e.x + o.x) * 0.5f, (k == 0 || k == N) ? 0.0f : (e.y + o.y) * 0.5f);
+}
 
-    const int fi = blockIdx.x;  // frame within this launch
-    const int s = blockIdx.y;
+template <int D>
+__global__ void __launch_bounds__(kVadThreads, D == 1 ? 2 : 1) vadfft_kernel(VadFftArgs a, const float2 *__restrict__ gT,
+                                                                const float *__restrict__ ghann, float norm) {
+    __shared__ float2 T[1024];
+    __shared__ float2 zb[kVadWarps][512 + 32];  // one pad slot per 16: the bit-reversed store (stride 16) spreads over all banks
+    __shared__ float2 hann2[512];
+
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < 1024; i += kVadThreads) T[i] = gT[i];
+    for (int i = tid; i < 512; i += kVadThreads) hann2[i] = reinterpret_cast<const float2 *>(ghann)[i];
     __syncthreads();
 
-    const long long frame = a.first_frame + fi;
-    const long long s0 = frame * 1024;                 // absolute start sample (input rate)
-    const long long rel = s0 - a.span_start;           // relative to the span start, may be negative
+    WarpFftTw<16, false> ftw;
+    ftw.init(T, lane);
+
     const size_t ypitch = kYLook + (size_t)kChunk16 * a.K;
+    const long long n_items = (long long)a.n_frames * a.S;
+    float2 *Z = zb[warp];
 
-    float bmin[kMaxBands];
+    for (long long item = (long long)blockIdx.x * kVadWarps + warp; item < n_items; item += (long long)gridDim.x * kVadWarps) {
+        const int fi = (int)(item % a.n_frames);  // frame within this launch (fastest: neighbouring warps read neighbouring audio)
+        const int s = (int)(item / a.n_frames);
+        const long long frame = a.first_frame + fi;
+        const long long s0 = frame * 1024;                 // absolute start sample (input rate)
+        const long long rel = s0 - a.span_start;           // relative to the span start, may be negative
+
+        float bmin[kMaxBands];
 #pragma unroll
-    for (int b = 0; b < kMaxBands; ++b) bmin[b] = 999.0f;
+        for (int b = 0; b < kMaxBands; ++b) bmin[b] = 999.0f;  // VADMachine.zig:153
 
-    for (int ch0 = 0; ch0 < a.C; ch0 += kVadWarps) {
-        const int ch = ch0 + warp;
-        if (ch < a.C) {
-            // y16 index 0 of the span sits at +kYLook; (rel + i) is the 48 k (input-rate) offset
+        for (int ch = 0; ch < a.C; ++ch) {
+            // y16 index 0 of the span sits at +kYLook; (rel + i) is the input-rate offset
             const float *__restrict__ y = a.y16 + (size_t)(s * a.C + ch) * ypitch + kYLook;
             float2 v[16];
 #pragma unroll
             for (int q = 0; q < 16; ++q) {
                 const int n = lane + 32 * q;
                 float e[2];
+                if (D == 1) {
+                    const float2 t = *reinterpret_cast<const float2 *>(y + rel + 2 * n);  // rel and the row pitch are even
+                    e[0] = t.x; e[1] = t.y;
+                } else {
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    const long long p = rel + 2 * n + j;
-                    float val;
-                    if (D == 1) {
-                        val = y[p];
-                    } else {
+                    for (int j = 0; j < 2; ++j) {
                         // resample.zig:44-59: position 3m+2 carries y16[m]; 3m and 3m+1 interpolate from y16[m-1]
+                        const long long p = rel + 2 * n + j;
                         const long long m = (p >= 0) ? p / D : -((-p + D - 1) / D);
                         const int ph = (int)(p - m * D);
                         const float cur = y[m];
-                        if (ph == D - 1) val = cur;
+                        if (ph == D - 1) e[j] = cur;
                         else {
                             const float prev = y[m - 1];
                             const float frac = __fdiv_rn((float)(ph + 1), (float)D);
-                            val = fmaf(cur - prev, frac, prev);
+                            e[j] = fmaf(cur - prev, frac, prev);
                         }
                     }
-                    e[j] = val;
                 }
-                const float2 w2 = __ldg(reinterpret_cast<const float2 *>(ghann) + n);
-                v[q] = make_float2(e[0] * w2.x, e[1] * w2.y);
+                const float2 hw = hann2[n];
+                v[q] = make_float2(e[0] * hw.x, e[1] * hw.y);
             }
-            warp_cfft<16, false>(v, T, lane);
+            warp_cfft_tw<16, false>(v, ftw);
 #pragma unroll
-            for (int k1 = 0; k1 < 16; ++k1) zb[warp][cfft_out_index<16>(lane, k1)] = v[k1];
+            for (int k1 = 0; k1 < 16; ++k1) Z[k1 + 17 * bitrev5(lane)] = v[k1];  // = pad(k1 + 16*bitrev5(lane))
             __syncwarp();
-            // magnitudes of the bins any band needs -> reuse zb's own storage is unsafe; use registers + shuffles:
-            // each band is at most a few dozen bins; lane 0 accumulates sequentially in index order.
             for (int b = 0; b < a.n_bands; ++b) {
                 const int lo = a.band_lo[b], hi = a.band_hi[b];
                 float acc = 0.0f;
-                for (int base = lo; base <= hi; base += 32) {
-                    const int k = base + lane;
-                    float mag = 0.0f;
-                    if (k <= hi) {
-                        const float2 X = rfft_bin(zb[warp], T, 512, k);
-                        // FFT.zig:16-18 abs = sqrt(r*r + i*i); BufferedFFT.zig:176 * norm_factor
-                        mag = __fmul_rn(sqrtf(__fadd_rn(__fmul_rn(X.x, X.x), __fmul_rn(X.y, X.y))), norm);
-                    }
-                    const int cnt = min(32, hi - base + 1);
-                    for (int j = 0; j < cnt; ++j) acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, mag, j));
+                for (int k = lo + lane; k <= hi; k += 32) {
+                    const float2 X = rfft_bin_padded(Z, T, 512, k);
+                    // FFT.zig:16-18 abs = sqrt(r*r + i*i); BufferedFFT.zig:176 * norm_factor
+                    acc += __fmul_rn(sqrtf(__fadd_rn(__fmul_rn(X.x, X.x), __fmul_rn(X.y, X.y))), norm);
                 }
-                if (lane == 0) chband[warp][b] = acc;
+#pragma unroll
+                for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+                bmin[b] = fminf(bmin[b], acc);
             }
             __syncwarp();
         }
-        __syncthreads();
-        if (tid == 0) {
-            for (int w = 0; w < kVadWarps && ch0 + w < a.C; ++w)
-                for (int b = 0; b < a.n_bands; ++b) bmin[b] = fminf(bmin[b], chband[w][b]);
+        if (lane == 0) {
+            for (int b = 0; b < a.n_bands; ++b) a.band[((size_t)b * a.S + s) * a.max_frames + fi] = bmin[b];
+            // VADMetadata merge over the (at most two) chunks this frame draws samples from
+            const int pitch = 1 + a.K;
+            const long long e0 = s0 + 1023;
+            const long long c_first = (s0 >= a.span_start) ? (rel / a.chunk) : -1;     // -1 = previous span's last chunk
+            const long long c_last = (e0 - a.span_start) / a.chunk;                    // e0 >= span_start always
+            float sum = 0.0f, wsum = 0.0f;
+            if (c_first == c_last) {
+                const float r = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_first + 1, a.chunk);
+                sum = __fmul_rn(r, 1024.0f);
+                wsum = 1024.0f;
+            } else {
+                const long long boundary = a.span_start + c_last * a.chunk;  // first sample of the later chunk
+                const float n0 = (float)(boundary - s0), n1 = (float)(s0 + 1024 - boundary);
+                const float r0 = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_first + 1, a.chunk);
+                const float r1 = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_last + 1, a.chunk);
+                sum = __fadd_rn(__fmul_rn(r0, n0), __fmul_rn(r1, n1));
+                wsum = __fadd_rn(n0, n1);
+            }
+            a.ratio[(size_t)s * a.max_frames + fi] = __fdiv_rn(sum, wsum);
         }
-        __syncthreads();
-    }
-    if (tid == 0) {
-        for (int b = 0; b < a.n_bands; ++b) a.band[((size_t)b * a.S + s) * a.max_frames + fi] = bmin[b];
-        // VADMetadata merge over the (at most two) chunks this frame draws samples from
-        const int pitch = 1 + a.K;
-        const long long e0 = s0 + 1023;
-        const long long c_first = (s0 >= a.span_start) ? (rel / a.chunk) : -1;     // -1 = previous span's last chunk
-        const long long c_last = (e0 - a.span_start) / a.chunk;                    // e0 >= span_start always
-        float sum = 0.0f, wsum = 0.0f;
-        if (c_first == c_last) {
-            const float r = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_first + 1, a.chunk);
-            sum = __fmul_rn(r, 1024.0f);
-            wsum = 1024.0f;
-        } else {
-            const long long boundary = a.span_start + c_last * a.chunk;  // first sample of the later chunk
-            const float n0 = (float)(boundary - s0), n1 = (float)(s0 + 1024 - boundary);
-            const float r0 = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_first + 1, a.chunk);
-            const float r1 = chunk_ratio(a.sumsq, a.C, s, pitch, (int)c_last + 1, a.chunk);
-            sum = __fadd_rn(__fmul_rn(r0, n0), __fmul_rn(r1, n1));
-            wsum = __fadd_rn(n0, n1);
-        }
-        a.ratio[(size_t)s * a.max_frames + fi] = __fdiv_rn(sum, wsum);
     }
 }
 
@@ -152,7 +164,8 @@ void launch_vadfft(const VadFftArgs &a, const Tables &t, cudaStream_t s) {
     if (a.n_frames <= 0 || a.S <= 0) return;
     if (a.n_bands > kMaxBands) throw Error(FVAD_ERR_INVALID_ARGUMENT, "too many distinct speech bands");
     if (a.fft_size != 1024) throw Error(FVAD_ERR_INVALID_FFT_SIZE, "GPU VAD path supports fft_size 1024");
-    dim3 grid((unsigned)a.n_frames, (unsigned)a.S);
+    const long long items = (long long)a.n_frames * a.S;
+    const unsigned grid = (unsigned)std::min<long long>((items + kVadWarps - 1) / kVadWarps, 148 * (a.D == 1 ? 2 : 1));
     if (a.D == 1) vadfft_kernel<1><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
     else if (a.D == 3) vadfft_kernel<3><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
     else throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "unsupported upsample factor");
