@@ -32,9 +32,12 @@ struct GemmShared {
 };
 
 struct GemmPlan {  // host-computed shared-memory plan
-    int KS, n_slabs, n_stages, stage_bytes, a_bytes, bias_off, sh_off, smem_bytes;
+    int KS, n_slabs, n_stages, stage_bytes, a_bytes, bias_off, tr_off, sh_off, smem_bytes;
 };
 
+// ACT: 0 none, 1 relu, 2 sigmoid.  OUT: 0 fp16 tiles for the next layer, 1 f32 gains rows (coalesced through a
+// per-warp shared-memory transpose).
+template <int ACT, int OUT>
 __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs a, const GemmPlan pl) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t *sA = smem, *sB = smem + pl.a_bytes;
@@ -97,7 +100,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
         // ===== MMA issuer =====
         if (elect_one()) {
             uint32_t st = 0, ph = 0, work = 0, im = 0;
-            const uint32_t sa0 = smem_u32(sA), sb0 = smem_u32(sB);
+            // descriptors as (lo, hi): the K loop advances lo by immediates (tc_dev.cuh, mma_ss_lohi)
+            const uint64_t ad0 = make_smem_desc(smem_u32(sA), kTileM * 16, 128);
+            const uint32_t alo0 = (uint32_t)ad0, ahi = (uint32_t)(ad0 >> 32);
             for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
                 for (int j = 0; j < a.n_tiles; ++j, ++work) {
                     const int NT = a.nt_size[j];
@@ -107,17 +112,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                     const uint32_t idesc = make_idesc_f16(kTileM, NT);
                     const uint32_t d = tmem + buf * 256;
                     const bool last_n = (j == a.n_tiles - 1);
+                    const uint32_t bstep = 2u * (uint32_t)NT;  // one K-step of B = 2 core columns = 2*NT*16 bytes
                     for (int sl = 0; sl < n_slabs; ++sl) {
                         if (j == 0) mbar_wait(&sh->a_full[sl], im & 1);
                         mbar_wait(&sh->full[st], ph);
                         tc_fence_after();
-                        const int k0 = sl * KS, kw = min(KS, a.K - k0);
-                        const uint32_t sa = sa0 + (k0 / 8) * (kTileM * 16), sb = sb0 + st * pl.stage_bytes;
-                        for (int kk = 0; kk < kw / 16; ++kk) {
-                            const uint64_t ad = make_smem_desc(sa + kk * 2 * (kTileM * 16), kTileM * 16, 128);
-                            const uint64_t bd = make_smem_desc(sb + kk * 2 * (NT * 16), NT * 16, 128);
-                            mma_ss(d, ad, bd, idesc, (sl > 0 || kk > 0) ? 1u : 0u);
-                        }
+                        const int k0 = sl * KS, nk = min(KS, a.K - k0) / 16;
+                        const uint64_t bd0 = make_smem_desc(smem_u32(sB + (size_t)st * pl.stage_bytes), NT * 16, 128);
+                        const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
+                        const uint32_t alo = alo0 + (uint32_t)(k0 / 8) * (kTileM * 16 / 16);
+                        if (sl == 0) mma_ss_lohi<false>(d, alo, ahi, blo, bhi, idesc);
+                        else mma_ss_lohi<true>(d, alo, ahi, blo, bhi, idesc);
+#pragma unroll
+                        for (int kk = 1; kk < 4; ++kk)
+                            if (kk < nk) mma_ss_lohi<true>(d, alo + kk * (2 * kTileM * 16 / 16), ahi, blo + kk * bstep, bhi, idesc);
                         mma_commit(&sh->empty[st]);               // B stage free once these MMAs have read it
                         if (last_n) mma_commit(&sh->a_empty[sl]); // A slab free for the next M-tile
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
@@ -131,20 +139,36 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
         const int wq = warp & 3;
         const int row = wq * 32 + lane;
         const size_t c_tile_bytes = tile_bytes(a.Nc);
+        float *tr = reinterpret_cast<float *>(smem + pl.tr_off) + wq * (32 * 33);  // OUT == 1: this warp's 32x32 transpose pad
         uint32_t work = 0;
+
+        // bias + activation of 8 consecutive columns starting at column `col` (absolute, multiple of 8)
+        auto act8 = [&](const uint32_t *r, int col, float (&v)[8]) {
+            const float4 b0 = *reinterpret_cast<const float4 *>(bias_s + col), b1 = *reinterpret_cast<const float4 *>(bias_s + col + 4);
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float x = __uint_as_float(r[i]) + b[i];
+                if (ACT == 1) x = fmaxf(x, 0.0f);
+                if (ACT == 2) x = __fdividef(1.0f, 1.0f + __expf(-x));
+                v[i] = x;
+            }
+        };
+
         for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x) {
             const int q = mt / a.T, t = mt % a.T;
             uint8_t *Ct = nullptr;
-            float *grow = nullptr;
-            if (a.out_mode == 0) {
+            float *g0 = nullptr;   // OUT == 1: gains row of this warp's first sequence
+            int rows_valid = 0;
+            if (OUT == 0) {
                 Ct = reinterpret_cast<uint8_t *>(a.C) + (size_t)(q * a.C_q + t + a.C_t0) * c_tile_bytes +
                      (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16;
             } else {
-                const int g = a.seq0 + q * kTileM + row;
-                if (g < a.n_seq) {
-                    const int sc = g / a.Kchunks, jc = g % a.Kchunks;
-                    grow = a.gains + ((size_t)sc * (kFrames * a.Kchunks) + (size_t)kFrames * jc + (t + a.C_t0)) * kBins;
-                }
+                // gains are [sc][50*Kchunks][161] and sequence g = sc*Kchunks + jc owns frames 50*jc.. of stream-channel
+                // sc, so its frame t is row 50*g + t of the flat [.][161] array: consecutive sequences are 50 rows apart
+                const int gq = a.seq0 + q * kTileM + wq * 32;
+                rows_valid = min(32, a.n_seq - gq);
+                g0 = a.gains + ((size_t)kFrames * gq + (t + a.C_t0)) * kBins;
             }
             for (int j = 0; j < a.n_tiles; ++j, ++work) {
                 const int NT = a.nt_size[j], col0 = a.nt_col[j];
@@ -152,29 +176,49 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                 mbar_wait(&sh->acc_full[buf], (work >> 1) & 1);
                 tc_fence_after();
                 const uint32_t tbase = tmem + buf * 256 + ((uint32_t)(wq * 32) << 16);
-                for (int c = 0; c < NT; c += 16) {
-                    uint32_t r[16];
-                    tmem_ld16(tbase + c, r);
-                    tmem_wait_ld();
-                    float v[16];
+                for (int c = 0; c < NT; c += 32) {
+                    uint32_t r[32];
+                    const bool full32 = c + 32 <= NT;  // N-tiles are multiples of 16
+                    if (full32) {
+                        tmem_ld32(tbase + c, r);
+                    } else {
+                        uint32_t r16[16];
+                        tmem_ld16(tbase + c, r16);
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float x = __uint_as_float(r[i]) + bias_s[col0 + c + i];
-                        if (a.act == 1) x = fmaxf(x, 0.0f);
-                        else if (a.act == 2) x = __fdividef(1.0f, 1.0f + __expf(-x));
-                        v[i] = x;
+                        for (int i = 0; i < 16; ++i) { r[i] = r16[i]; r[16 + i] = 0; }
                     }
-                    if (a.out_mode == 0) {
-                        uint4 lo, hi;
-                        lo.x = pack_h2(v[0], v[1]); lo.y = pack_h2(v[2], v[3]); lo.z = pack_h2(v[4], v[5]); lo.w = pack_h2(v[6], v[7]);
-                        hi.x = pack_h2(v[8], v[9]); hi.y = pack_h2(v[10], v[11]); hi.z = pack_h2(v[12], v[13]); hi.w = pack_h2(v[14], v[15]);
-                        uint8_t *p = Ct + (size_t)((col0 + c) >> 3) * (kTileM * 16);
-                        *reinterpret_cast<uint4 *>(p) = lo;
-                        *reinterpret_cast<uint4 *>(p + kTileM * 16) = hi;
-                    } else if (grow) {
+                    tmem_wait_ld();
+                    const int ng = full32 ? 4 : 2;  // groups of 8 columns
+                    if (OUT == 0) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (col0 + c + i < a.n_valid) grow[col0 + c + i] = v[i];
+                        for (int gI = 0; gI < 4; ++gI) {
+                            if (gI < ng) {
+                                float v[8];
+                                act8(r + 8 * gI, col0 + c + 8 * gI, v);
+                                uint4 o;
+                                o.x = pack_h2(v[0], v[1]); o.y = pack_h2(v[2], v[3]); o.z = pack_h2(v[4], v[5]); o.w = pack_h2(v[6], v[7]);
+                                *reinterpret_cast<uint4 *>(Ct + (size_t)(((col0 + c) >> 3) + gI) * (kTileM * 16)) = o;
+                            }
+                        }
+                    } else {
+                        // thread = row: park the 32 columns in shared memory, then every lane writes one column of each
+                        // row so a row's 32 floats leave as one 128-byte store
+#pragma unroll
+                        for (int gI = 0; gI < 4; ++gI) {
+                            if (gI < ng) {
+                                float v[8];
+                                act8(r + 8 * gI, col0 + c + 8 * gI, v);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) tr[lane * 33 + 8 * gI + i] = v[i];
+                            }
+                        }
+                        __syncwarp();
+                        const int col = col0 + c + lane;
+                        if (col < a.n_valid && lane < 8 * ng) {
+                            float *gp = g0 + col;
+                            for (int rr = 0; rr < rows_valid; ++rr) gp[(size_t)rr * (kFrames * kBins)] = tr[rr * 33 + lane];
+                        }
+                        __syncwarp();
                     }
                 }
                 tc_fence_before();
@@ -190,18 +234,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
 
 }  // namespace
 
-void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
+template <int ACT, int OUT>
+static void launch_variant(const GemmArgs &a, const GemmPlan &pl, int grid, cudaStream_t s) {
     static bool attr = false;
     if (!attr) {
-        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<ACT, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
         attr = true;
     }
+    tc_gemm_kernel<ACT, OUT><<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
+}
+
+void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     if (a.mt_count <= 0) return;
     GemmPlan pl;
     int nt_max = 0;
     for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
     pl.a_bytes = a.K * 256;  // K/8 core columns x 2048 B
-    const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + 1024;
+    const int tr_bytes = a.out_mode == 1 ? 4 * 32 * 33 * 4 : 0;
+    const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 1024;
     pl.KS = 64;
     for (;;) {
         pl.stage_bytes = nt_max * pl.KS * 2;
@@ -213,10 +263,16 @@ void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     pl.n_slabs = (a.K + pl.KS - 1) / pl.KS;
     if (pl.n_stages < 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: layer does not fit the shared-memory plan");
     pl.bias_off = pl.a_bytes + pl.n_stages * pl.stage_bytes;
-    pl.sh_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
+    pl.tr_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
+    pl.sh_off = pl.tr_off + tr_bytes;
     pl.smem_bytes = pl.sh_off + 1024;
     const int grid = a.mt_count < n_sm ? a.mt_count : n_sm;
-    tc_gemm_kernel<<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
+    if (a.out_mode == 1) {
+        if (a.act != 2) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: the gains output applies the sigmoid");
+        launch_variant<2, 1>(a, pl, grid, s);
+    } else if (a.act == 0) launch_variant<0, 0>(a, pl, grid, s);
+    else if (a.act == 1) launch_variant<1, 0>(a, pl, grid, s);
+    else throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: unsupported activation/output combination");
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
 }

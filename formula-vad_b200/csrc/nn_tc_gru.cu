@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (elect_one()) {
-            const uint32_t idesc = make_idesc_f16(kTileM, kChunkRows);
+            constexpr uint32_t idesc = make_idesc_f16(kTileM, kChunkRows);
             uint32_t it = 0, step = 0, use[2] = {0, 0};
             for (int iq = 0; iq < n_q; ++iq)
                 for (int t = 0; t < kSteps; ++t, ++step) {
@@ -101,12 +101,13 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
                         mbar_wait(&sh->full[st], (it / kRStages) & 1);
                         tc_fence_after();
                         const uint32_t d = tmem + (g ? kColAcc1 : kColAcc0);
-                        const uint32_t sb = smem_u32(smem + st * kRChunkBytes);
-#pragma unroll 5
-                        for (int kk = 0; kk < kH / 16; ++kk) {
-                            const uint64_t bd = make_smem_desc(sb + kk * 2 * (kChunkRows * 16), kChunkRows * 16, 128);
-                            mma_ts(d, hold + kk * 8, bd, idesc, kk > 0 ? 1u : 0u);
-                        }
+                        // K-step kk reads h columns [8kk, 8kk+8) and the R slab 1536 bytes (96 descriptor units) further
+                        const uint64_t bd0 = make_smem_desc(smem_u32(smem + st * kRChunkBytes), kChunkRows * 16, 128);
+                        const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
+                        mma_ts_lohi<false>(d, hold, blo, bhi, idesc);
+#pragma unroll
+                        for (int kk = 1; kk < kH / 16; ++kk)
+                            mma_ts_lohi<true>(d, hold + kk * 8, blo + kk * (2 * kChunkRows), bhi, idesc);
                         mma_commit(&sh->empty[st]);
                         mma_commit(&sh->acc_full[g]);
                     }
