@@ -55,7 +55,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -92,8 +92,8 @@ class ClockSampler:
         # "under load": samples whose power is above the median idle-ish floor
         thr = 0.5 * max(pw)
         load = [s for s, p in zip(sm, pw) if p >= thr] or sm
-        return {"sm_mhz": float(np.median(load)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
-                "samples": len(sm), "reasons": sorted(reasons)}
+        return {"sm_mhz": float(np.median(load)), "sm_mhz_min": float(min(load)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "power_w_median": float(np.median([p for p in pw if p >= thr] or pw)), "samples": len(sm), "reasons": sorted(reasons)}
 
 
 # ------------------------------------------------------------------------------------------------

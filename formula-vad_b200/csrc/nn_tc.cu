@@ -4,6 +4,9 @@
 //     pack -> fc1 -> W1 x -> GRU1 -> W2 h1 -> GRU2 -> fc2 -> fc3 -> fc4 (gains scatter)
 // and the activation workspace.  Kernels: nn_tc_gemm.cu, nn_tc_gru.cu.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
 #include <cstring>
 
 #include "nn.cuh"
@@ -100,6 +103,9 @@ public:
         FVAD_CUDA_CHECK(cudaGetDevice(&dev));
         FVAD_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
         fc1_relu_ = w.fc1_relu;
+        if (const char *e = getenv("FVAD_GRU_PAIR")) pair_ = atoi(e) != 0;
+        if (const char *e = getenv("FVAD_NN_TIMING")) timing_ = atoi(e) != 0;
+        if (timing_) for (auto &e : tev_) FVAD_CUDA_CHECK(cudaEventCreate(&e));
         const int H = 400;
         // gate-row permutation: p = 48c + 16g + u  <-  g*400 + 16c + u
         std::vector<int> perm(3 * H);
@@ -123,6 +129,16 @@ public:
             }
             gR_[l].ensure(img.size());
             FVAD_CUDA_CHECK(cudaMemcpy(gR_[l].p, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+            // CTA-pair image (nn_tc_gru2.cu): chunk c = [rows 0..23 | rows 24..47], each half tiled with R = 24
+            std::vector<__half> img2((size_t)3 * H * H);
+            for (int p = 0; p < 3 * H; ++p) {
+                const int c = p / 48, n = p % 48, half = n / 24, src = perm[(size_t)p];
+                uint8_t *base = reinterpret_cast<uint8_t *>(img2.data()) + ((size_t)c * 48 + (size_t)half * 24) * H * 2;
+                for (int k = 0; k < H; ++k)
+                    *reinterpret_cast<__half *>(base + tc::tiled_off(n % 24, k, 24)) = __float2half_rn(w.gru_R[l][(size_t)src * H + k]);
+            }
+            gR2_[l].ensure(img2.size());
+            FVAD_CUDA_CHECK(cudaMemcpy(gR2_[l].p, img2.data(), img2.size() * sizeof(__half), cudaMemcpyHostToDevice));
             gRbn_[l].ensure((size_t)H);
             FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
         }
@@ -146,24 +162,74 @@ public:
         for (int q0 = 0; q0 < q_total; q0 += QB) {
             const int Q = std::min(QB, q_total - q0);
             tc::PackArgs pa{sp.feat, a0_.p, Q, q0 * tc::kTileM, total, sp.K};
+            mark(0, s);
             tc::launch_tc_pack(pa, s);
+            mark(1, s);
             gemm(fc1_, a0_.p, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
+            mark(2, s);
             gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
-            tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[0].p, gRbn_[0].p, h1_.p, Q, 0}, n_sm_, s);
+            mark(3, s);
+            gru(0, h1_.p, Q, 0, s);
+            mark(4, s);
             gemm(gW_[1], h1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
-            tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[1].p, gRbn_[1].p, h2_.p, Q, kCtx}, n_sm_, s);
+            mark(5, s);
+            gru(1, h2_.p, Q, kCtx, s);
+            mark(6, s);
             gemm(fc2_, h2_.p, f2_.p, Q, kFrames, kSteps, kCtx, kFrames, 0, 1, s);
+            mark(7, s);
             gemm(fc3_, f2_.p, f3_.p, Q, kFrames, kFrames, 0, kFrames, 0, 1, s);
+            mark(8, s);
             GemmArgs g = base_args(fc4_, f3_.p, nullptr, Q, kFrames, kFrames, 0, kFrames, 0, 2);
             g.out_mode = 1; g.gains = sp.gains; g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
             tc::launch_tc_gemm(g, n_sm_, s);
+            mark(9, s);
+            collect(s);
         }
+    }
+
+    ~NnTc() override {
+        if (!timing_) return;
+        static const char *nm[9] = {"pack", "fc1", "W1", "gru1", "W2", "gru2", "fc2", "fc3", "fc4"};
+        double tot = 0;
+        for (double v : acc_ms_) tot += v;
+        fprintf(stderr, "[fvad nn timing] total %.2f ms:", tot);
+        for (int i = 0; i < 9; ++i) fprintf(stderr, " %s %.2f (%.0f%%)", nm[i], acc_ms_[i], 100.0 * acc_ms_[i] / (tot > 0 ? tot : 1));
+        fprintf(stderr, "\n");
+        for (auto &e : tev_) cudaEventDestroy(e);
     }
 
 private:
     int n_sm_ = 148, fc1_relu_ = 0;
     Layer fc1_, gW_[2], fc2_, fc3_, fc4_;
-    DevBuf<__half> gR_[2];
+    DevBuf<__half> gR_[2], gR2_[2];
+    // FVAD_NN_TIMING=1: CUDA-event time per layer kernel, summed over the handle's lifetime (adds a sync per sub-batch)
+    bool timing_ = false;
+    cudaEvent_t tev_[10] = {};
+    double acc_ms_[9] = {};
+    void mark(int i, cudaStream_t s) { if (timing_) cudaEventRecord(tev_[i], s); }
+    void collect(cudaStream_t s) {
+        if (!timing_) return;
+        cudaStreamSynchronize(s);
+        for (int i = 0; i < 9; ++i) { float ms = 0; cudaEventElapsedTime(&ms, tev_[i], tev_[i + 1]); acc_ms_[i] += ms; }
+    }
+    DevBuf<unsigned long long> trace_;
+    bool traced_ = false;
+    bool pair_ = false;  // CTA-pair GRU (FVAD_GRU_PAIR=0 selects the one-CTA kernel, kept for A/B measurements)
+
+    void gru(int l, __half *hout, int Q, int t_store_min, cudaStream_t s) {
+        unsigned long long *tr = nullptr;
+        const char *tp = getenv("FVAD_GRU_TRACE");
+        if (tp && l == 0 && !traced_) { trace_.ensure(54 * 25 * 8); FVAD_CUDA_CHECK(cudaMemsetAsync(trace_.p, 0, 54 * 25 * 8 * 8, s)); tr = trace_.p; }
+        if (pair_) tc::launch_tc_gru2(tc::GruArgs{xp_.p, gR2_[l].p, gRbn_[l].p, hout, Q, t_store_min, nullptr}, n_sm_, s);
+        else tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[l].p, gRbn_[l].p, hout, Q, t_store_min, tr}, n_sm_, s);
+        if (tr) {  // debug only: dump CTA 0's timeline of the first GRU launch
+            traced_ = true;
+            std::vector<unsigned long long> h(54 * 25 * 8);
+            FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
+            FVAD_CUDA_CHECK(cudaMemcpy(h.data(), trace_.p, h.size() * 8, cudaMemcpyDeviceToHost));
+            if (FILE *f = fopen(tp, "wb")) { fwrite(h.data(), 8, h.size(), f); fclose(f); }
+        }
+    }
     DevBuf<float> gRbn_[2];
     DevBuf<__half> a0_, x1_, xp_, h1_, h2_, f2_, f3_;
 

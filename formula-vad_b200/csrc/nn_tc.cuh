@@ -51,8 +51,11 @@ struct GruArgs {
     const float *rbn;
     __half *hout;
     int Q, t_store_min;
+    unsigned long long *trace;  // debug (FVAD_GRU_TRACE): CTA 0 logs clock64 at [step][chunk][event], nullptr otherwise
 };
 void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
+// CTA-pair version (nn_tc_gru2.cu): Rimg is the split image (per chunk two 24-row halves tiled with R = 24)
+void launch_tc_gru2(const GruArgs &a, int n_sm, cudaStream_t s);
 
 // features f32 [SC][4+50K][161] -> fp16 tiles [q][54] of 176 columns for sequences seq0 .. seq0+128*Q-1
 struct PackArgs {

@@ -20,6 +20,9 @@ namespace tc {
 
 namespace {
 
+// timeline probe: event e of (step t, chunk c) of the first tile of CTA 0
+#define GRU_TRACE(e, t, c) do { if (a.trace && blockIdx.x == 0 && iq == 0) a.trace[((t) * 25 + (c)) * 8 + (e)] = (unsigned long long)clock64(); } while (0)
+
 constexpr int kH = 400;
 constexpr int kChunkUnits = 16;
 constexpr int kChunkRows = 48;
@@ -35,11 +38,17 @@ struct GruShared {
     uint32_t tmem_base;
 };
 
-__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float tanh_fast(float x) {
-    // tanh(x) = 1 - 2/(1+exp(2x)); exp overflow gives 1 - 0 = 1, underflow gives 1 - 2 = -1
-    return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x));
+// Gate activations on the hardware tanh (MUFU.TANH, tanh.approx.f32: relative error ~2^-11, the rounding
+// step of the fp16 hidden state these gates feed): sigma(x) = 0.5 + 0.5*tanh(x/2).  One special-function op per
+// gate instead of ex2 + rcp -- the epilogue warps, not the tensor pipe, bound this kernel (ncu: XU pipe and
+// issue slots), so this halves their work.  The fp32 backend (nn_f32.cu) keeps expf/tanhf.
+__device__ __forceinline__ float tanh_hw(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_hw(0.5f * x), 0.5f); }
+__device__ __forceinline__ float tanh_fast(float x) { return tanh_hw(x); }
 
 __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -82,25 +91,32 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
                         bulk_g2s(smem + st * kRChunkBytes, R + (size_t)c * kRChunkBytes, kRChunkBytes, &sh->full[st]);
                     }
         }
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
+    } else if (warp == 1 || warp == 3) {
+        // ===== MMA issuers: warp 1 issues the even chunks (accumulator 0), warp 3 the odd ones (accumulator 1) =====
+        // One issuing thread spends ~520 cycles pushing a chunk's 25 MMAs and ~400 more on its two barrier waits,
+        // commits and loop overhead (timeline: tools/gru_trace.py) -- alone it leaves the tensor pipe idle a third of
+        // the time.  Two threads alternate, so one's bookkeeping hides under the other's issue burst.  The chunks
+        // are independent (separate accumulators, separate R stages); each thread's commits cover its own MMAs.
         if (elect_one()) {
             constexpr uint32_t idesc = make_idesc_f16(kTileM, kChunkRows);
-            uint32_t it = 0, step = 0, use[2] = {0, 0};
+            const uint32_t g = warp == 1 ? 0u : 1u;
+            const uint32_t d = tmem + (g ? kColAcc1 : kColAcc0);
+            uint32_t step = 0, use = 0;
             for (int iq = 0; iq < n_q; ++iq)
                 for (int t = 0; t < kSteps; ++t, ++step) {
                     // h_{t-1} complete in TMEM (epilogue warps of the previous step / the zero fill)
                     mbar_wait(&sh->h_ready, step & 1);
                     tc_fence_after();
+                    if (g == 0) GRU_TRACE(6, t, 0);
                     const uint32_t hold = tmem + ((t & 1) ? kColH1 : kColH0);
-                    for (int c = 0; c < kChunks; ++c, ++it) {
-                        const uint32_t g = c & 1;
-                        mbar_wait(&sh->acc_empty[g], (use[g] & 1) ^ 1);
-                        ++use[g];
-                        const int st = it % kRStages;
+                    for (int c = (int)g; c < kChunks; c += 2) {
+                        const uint32_t it = step * kChunks + (uint32_t)c;
+                        const uint32_t st = it % kRStages;
                         mbar_wait(&sh->full[st], (it / kRStages) & 1);
+                        mbar_wait(&sh->acc_empty[g], (use & 1) ^ 1);
+                        ++use;
                         tc_fence_after();
-                        const uint32_t d = tmem + (g ? kColAcc1 : kColAcc0);
+                        GRU_TRACE(1, t, c);
                         // K-step kk reads h columns [8kk, 8kk+8) and the R slab 1536 bytes (96 descriptor units) further
                         const uint64_t bd0 = make_smem_desc(smem_u32(smem + st * kRChunkBytes), kChunkRows * 16, 128);
                         const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
@@ -110,6 +126,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
                             mma_ts_lohi<true>(d, hold + kk * 8, blo + kk * (2 * kChunkRows), bhi, idesc);
                         mma_commit(&sh->empty[st]);
                         mma_commit(&sh->acc_full[g]);
+                        GRU_TRACE(2, t, c);
                     }
                 }
         }
@@ -154,6 +171,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
                     mbar_wait(&sh->acc_full[g], use & 1);
                     ++use;
                     tc_fence_after();
+                    if (wq == 0 && lane == 0) GRU_TRACE(3, t, c);
                     uint32_t az[16], ar[16], an[16], ho[8];
                     tmem_ld16(acc, az);
                     tmem_ld16(acc + 16, ar);
@@ -163,6 +181,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&sh->acc_empty[g]);  // accumulator drained: the next chunk's MMAs may start
+                    if (wq == 0 && lane == 0) GRU_TRACE(4, t, c);
 
                     const uint32_t *xw = reinterpret_cast<const uint32_t *>(x);  // 24 words: z[0..7] r[8..15] n[16..23] (pairs)
                     uint32_t hn[8];
@@ -182,6 +201,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a)
                         hn[p] = pack_h2(h0, h1);
                     }
                     tmem_st8(hnew + c * 8, hn);
+                    if (wq == 0 && lane == 0) GRU_TRACE(5, t, c);
                     if (store) {
                         uint8_t *p = hot + (size_t)(c * 2) * (kTileM * 16);
                         *reinterpret_cast<uint4 *>(p) = make_uint4(hn[0], hn[1], hn[2], hn[3]);

@@ -198,6 +198,48 @@ __device__ __forceinline__ void mma_commit_mc(uint64_t *bar, uint16_t mask) {
                  : "memory");
 }
 
+// ---- CTA-pair (cta_group::2) forms: one MMA spans the two SMs of a cluster of 2.  M = 256 (each CTA's TMEM
+// holds its own 128 rows of A and D at the same address), B is split along N: each CTA's shared memory holds
+// N/2 rows at the same offset.  Only the leader (cluster rank 0) issues; commits multicast to both CTAs.
+template <uint32_t NCOLS>
+__device__ __forceinline__ void tmem_alloc2(uint32_t *slot_in_smem) {  // one whole warp in EACH CTA of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_in_smem)), "n"(NCOLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t NCOLS>
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(NCOLS) : "memory");
+}
+template <bool ACC>
+__device__ __forceinline__ void mma2_ts_lohi(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .b64 bd;\n\t.reg .pred p;\n\t"
+        "setp.eq.u32 p, 1, %5;\n\t"
+        "mov.b64 bd, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], bd, %4, p;\n\t}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "n"(ACC ? 1 : 0)
+        : "memory");
+}
+template <bool ACC>
+__device__ __forceinline__ void mma2_ss_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .b64 ad, bd;\n\t.reg .pred p;\n\t"
+        "setp.eq.u32 p, 1, %6;\n\t"
+        "mov.b64 ad, {%1, %2};\n\t"
+        "mov.b64 bd, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], ad, bd, %5, p;\n\t}\n" ::"r"(d_tmem),
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "n"(ACC ? 1 : 0)
+        : "memory");
+}
+// all MMAs issued so far by this thread arrive on the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void mma2_commit_mc(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"(mask)
+                 : "memory");
+}
+
 // TMEM -> registers: this warp's 32 lanes x N consecutive 32-bit columns (thread = lane/row)
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
