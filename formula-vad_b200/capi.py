@@ -77,7 +77,23 @@ EXPORTS = (
     "fvad_pipeline_destroy", "fvad_pipeline_push_samples", "fvad_pipeline_total_write_count",
     "fvad_pipeline_segments", "fvad_batch_options_default", "fvad_batch_create", "fvad_batch_destroy",
     "fvad_batch_push", "fvad_batch_push_i16", "fvad_batch_segments", "fvad_batch_tap", "fvad_batch_stats_get",
+    "fvad_eval_config_default", "fvad_evaluate", "fvad_batch_evaluate",
 )
+
+
+class EvalSegment(C.Structure):  # fvad_eval_segment
+    _fields_ = [("from_sec", C.c_float), ("to_sec", C.c_float)]
+
+
+class EvalConfig(C.Structure):  # fvad_eval_config
+    _fields_ = [("ignore_shorter_than_sec", C.c_float), ("extrude_start", C.c_float), ("extrude_end", C.c_float),
+                ("fill_gaps", C.c_float), ("f_score_beta", C.c_float)]
+
+
+class EvalStats(C.Structure):  # fvad_eval_stats
+    _fields_ = [(n, C.c_float) for n in ("total_positives_sec", "true_positives_sec", "false_positives_sec",
+                                          "false_negatives_sec", "true_positive_rate", "precision",
+                                          "false_negative_rate", "false_discovery_rate", "f_score", "fm_index")]
 
 
 class FvadError(RuntimeError):
@@ -139,6 +155,9 @@ def lib():
     sig("fvad_batch_segments", i32, vp, sz, sz, C.POINTER(C.POINTER(Segment)), C.POINTER(sz))
     sig("fvad_batch_tap", i32, vp, i32, vp, sz, C.POINTER(sz))
     sig("fvad_batch_stats_get", i32, vp, C.POINTER(BatchStats))
+    sig("fvad_eval_config_default", None, C.POINTER(EvalConfig))
+    sig("fvad_evaluate", i32, C.POINTER(EvalSegment), sz, C.POINTER(EvalSegment), sz, C.POINTER(EvalConfig), C.POINTER(EvalStats))
+    sig("fvad_batch_evaluate", i32, vp, C.POINTER(EvalSegment), C.POINTER(sz), C.POINTER(EvalConfig), C.POINTER(EvalStats))
     _lib = L
     return L
 

@@ -422,4 +422,32 @@ int fvad_batch_stats_get(fvad_batch *b, fvad_batch_stats *out) {
     });
 }
 
+void fvad_eval_config_default(fvad_eval_config *cfg) {
+    if (!cfg) return;
+    cfg->ignore_shorter_than_sec = 0.0f;
+    cfg->extrude_start = 0.0f;
+    cfg->extrude_end = 0.0f;
+    cfg->fill_gaps = 0.0f;
+    cfg->f_score_beta = 0.7f;  // statistics.zig:108
+}
+
+int fvad_evaluate(const fvad_eval_segment *vad, size_t n_vad, const fvad_eval_segment *ref, size_t n_ref,
+                  const fvad_eval_config *cfg, fvad_eval_stats *out) {
+    return guarded([&] {
+        fvad_eval_config c;
+        fvad_eval_config_default(&c);
+        evaluate_lists(vad, n_vad, ref, n_ref, cfg ? *cfg : c, out);
+    });
+}
+
+int fvad_batch_evaluate(fvad_batch *b, const fvad_eval_segment *refs, const size_t *ref_offsets, const fvad_eval_config *cfg,
+                        fvad_eval_stats *out) {
+    return guarded([&] {
+        if (!b) throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL handle");
+        fvad_eval_config c;
+        fvad_eval_config_default(&c);
+        b->impl->evaluate(refs, ref_offsets, cfg ? *cfg : c, out);
+    });
+}
+
 }  // extern "C"

@@ -7,6 +7,7 @@
 // passes is the halo set of SURVEY App. B (160 input samples, 4 feature rows, 160 output samples,
 // 1024 denoised samples, one chunk ratio, the VAD machine states).
 #pragma once
+#include <algorithm>
 #include <array>
 #include <memory>
 #include <vector>
@@ -33,6 +34,8 @@ public:
     void segments(size_t stream, size_t machine, const fvad_segment **segs, size_t *n);
     size_t tap(int which, void *dst, size_t dst_bytes);
     void stats(fvad_batch_stats *out) const;
+    // eval.cu: statistics of every (stream, machine) list against the streams' reference segments; out [S][M]
+    void evaluate(const fvad_eval_segment *refs, const size_t *ref_offsets, const fvad_eval_config &cfg, fvad_eval_stats *out);
     uint64_t total_write_count() const { return total_written_; }
     size_t n_machines() const { return (size_t)M_; }
     size_t n_streams() const { return (size_t)S_; }
@@ -106,5 +109,9 @@ private:
     uint64_t launches0_ = 0, chunks_processed_ = 0;
     double last_ms_[6] = {};
 };
+
+// eval.cu: one pair of lists (host pointers)
+void evaluate_lists(const fvad_eval_segment *vad, size_t n_vad, const fvad_eval_segment *ref, size_t n_ref,
+                    const fvad_eval_config &cfg, fvad_eval_stats *out);
 
 }  // namespace fvad

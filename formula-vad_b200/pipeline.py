@@ -220,6 +220,48 @@ class AudioPipeline:
     __del__ = deinit
 
 
+def eval_config(**kw) -> capi.EvalConfig:
+    """StatConfig defaults of the reference (Evaluator/statistics.zig:77-83, beta 0.7) with overrides."""
+    c = capi.EvalConfig()
+    capi.lib().fvad_eval_config_default(C.byref(c))
+    for k, v in kw.items():
+        if not hasattr(c, k):
+            raise AttributeError(k)
+        setattr(c, k, v)
+    return c
+
+
+def _eval_segs(segs):
+    arr = (capi.EvalSegment * max(len(segs), 1))()
+    for i, (a, b) in enumerate(segs):
+        arr[i].from_sec, arr[i].to_sec = a, b
+    return arr
+
+
+def _stats_dict(st) -> dict:
+    return {k: getattr(st, k) for k, _ in capi.EvalStats._fields_}
+
+
+class Evaluator:
+    """Mirror of src/Evaluator.zig + Evaluator/statistics.zig: `Evaluator.init_and_run(vad, ref).stats(cfg)`.
+    Segments are (from_sec, to_sec) pairs."""
+
+    def __init__(self, input_segments, reference_segments):
+        self.input_segments, self.reference_segments = list(input_segments), list(reference_segments)
+
+    @classmethod
+    def init_and_run(cls, input_segments, reference_segments):
+        return cls(input_segments, reference_segments)
+
+    def stats(self, config: capi.EvalConfig | None = None) -> dict:
+        st = capi.EvalStats()
+        cfg = config if config is not None else eval_config()
+        check(capi.lib().fvad_evaluate(_eval_segs(self.input_segments), len(self.input_segments),
+                                       _eval_segs(self.reference_segments), len(self.reference_segments),
+                                       C.byref(cfg), C.byref(st)))
+        return _stats_dict(st)
+
+
 class BatchPipeline:
     """n_streams independent AudioPipelines advanced in lock step on one GPU."""
     _h = None
@@ -286,6 +328,18 @@ class BatchPipeline:
         if which in (capi.TAP_DENOISED16, capi.TAP_DENOISED):
             return out.reshape(sc, -1)
         return out.reshape(self.n_streams, -1)
+
+    def evaluate(self, references, config: capi.EvalConfig | None = None):
+        """references: per stream a list of (from_sec, to_sec).  Returns [stream][machine] dicts of SingleStats."""
+        assert len(references) == self.n_streams
+        flat = [seg for r in references for seg in r]
+        off = (C.c_size_t * (self.n_streams + 1))()
+        for s, r in enumerate(references):
+            off[s + 1] = off[s] + len(r)
+        out = (capi.EvalStats * (self.n_streams * self.n_machines))()
+        cfg = config if config is not None else eval_config()
+        check(self._L.fvad_batch_evaluate(self._h, _eval_segs(flat), off, C.byref(cfg), out))
+        return [[_stats_dict(out[s * self.n_machines + m]) for m in range(self.n_machines)] for s in range(self.n_streams)]
 
     def stats(self) -> dict:
         st = capi.BatchStats()

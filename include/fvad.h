@@ -216,6 +216,24 @@ FVAD_API int fvad_batch_segments(fvad_batch *b, size_t stream, size_t machine, c
 FVAD_API int fvad_batch_tap(fvad_batch *b, int tap, void *dst, size_t dst_bytes, size_t *n_elements);
 FVAD_API int fvad_batch_stats_get(fvad_batch *b, fvad_batch_stats *out);
 
+/* ------------------------------------------------------------------------------------------
+ * Evaluator -- replaces src/Evaluator.zig + src/Evaluator/statistics.zig (segment matching, TP/FP/FN
+ * seconds, rates, F-score, Fowlkes-Mallows), f32 arithmetic in the reference's summation order.
+ * ---------------------------------------------------------------------------------------- */
+/* statistics.zig:77-83 defaults, beta = 0.7 */
+FVAD_API void fvad_eval_config_default(fvad_eval_config *cfg);
+/* Evaluator.initAndRun (Evaluator.zig:90-156) + statistics.fromEvaluator (statistics.zig:85-114) for one pair
+ * of lists (host pointers, any order: both are sorted by start like the reference does). */
+FVAD_API int fvad_evaluate(const fvad_eval_segment *vad, size_t n_vad, const fvad_eval_segment *reference, size_t n_reference,
+                           const fvad_eval_config *cfg, fvad_eval_stats *out);
+/* The same for every (stream, machine) of a batch in one launch, straight from the device-resident segment
+ * lists (sample indices become seconds as f32(sample)/f32(sample_rate), SimulationInstance.zig:236-239).
+ * references: all streams' labelled segments concatenated; reference_offsets[n_streams+1] delimits them.
+ * out: [n_streams][n_machines].  This is the scoring half of the config sweep `alt_vad_machine_configs`
+ * exists for (VADPipeline.zig:24). */
+FVAD_API int fvad_batch_evaluate(fvad_batch *b, const fvad_eval_segment *references, const size_t *reference_offsets,
+                                 const fvad_eval_config *cfg, fvad_eval_stats *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,35 @@ typedef struct fvad_config {
     int32_t skip_processing;
 } fvad_config;
 
+/* src/Evaluator/SpeechSegment.zig:7-9  `from_sec`, `to_sec` (the other fields are links and report text) */
+typedef struct fvad_eval_segment {
+    float from_sec;
+    float to_sec;
+} fvad_eval_segment;
+
+/* src/Evaluator/statistics.zig:77-83  `StatConfig` (+ the F-score beta the reference fixes at 0.7, :108) */
+typedef struct fvad_eval_config {
+    float ignore_shorter_than_sec; /* 0 */
+    float extrude_start;           /* 0 */
+    float extrude_end;             /* 0 */
+    float fill_gaps;               /* 0 */
+    float f_score_beta;            /* 0.7 */
+} fvad_eval_config;
+
+/* src/Evaluator/statistics.zig:6-41  `SingleStats` (same field names) */
+typedef struct fvad_eval_stats {
+    float total_positives_sec;
+    float true_positives_sec;
+    float false_positives_sec;
+    float false_negatives_sec;
+    float true_positive_rate;
+    float precision;
+    float false_negative_rate;
+    float false_discovery_rate;
+    float f_score;
+    float fm_index;
+} fvad_eval_stats;
+
 /* NSNet2 constants, src/NSNet2.zig:12-16 */
 enum {
     FVAD_NS_NFFT = 320,
