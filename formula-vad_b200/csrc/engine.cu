@@ -398,10 +398,21 @@ void Batch::push_any(const void *const *pcm, size_t n_pointers, size_t n, int me
         } else if (nbuf == 2 && !d_sptr_[1].p) {
             throw Error(FVAD_ERR_CUDA, "stage pointer table missing");
         }
-        size_t span = 0;
-        for (size_t k0 = 0; k0 < Ktot; k0 += Kst, ++span) {
+        // Span schedule: full spans, except a short first one (its copy cannot overlap any compute) and a short
+        // last one (its compute cannot overlap any copy) when the push is long enough to have several.
+        std::vector<size_t> sched;
+        {
+            const size_t ramp = std::max<size_t>(Kst / 8, 1);
+            size_t rem = Ktot;
+            if (Ktot > Kst && !opt_.max_span_chunks) { sched.push_back(ramp); rem -= ramp; }
+            while (rem > Kst) { sched.push_back(Kst); rem -= Kst; }
+            if (rem > 2 * ramp && Ktot > Kst && !opt_.max_span_chunks) { sched.push_back(rem - ramp); rem = ramp; }
+            if (rem) sched.push_back(rem);
+        }
+        size_t k0 = 0;
+        for (size_t span = 0; span < sched.size(); k0 += sched[span], ++span) {
             const int b = (int)(span & 1) % nbuf;
-            const size_t K = std::min<size_t>(Kst, Ktot - k0);
+            const size_t K = sched[span];
             const size_t need = K * (size_t)chunk_;
             const size_t from_pend = (k0 == 0) ? (size_t)n_pend_ : 0;
             FVAD_CUDA_CHECK(cudaStreamWaitEvent(cs, stage_free_[b], 0));  // the span that last used buffer b is done
