@@ -222,11 +222,14 @@ def run_native(args):
     t0 = time.perf_counter()
     dev_ms = 0.0
     stage = np.zeros(5)
+    layer_ms, layer_n = np.zeros(9), np.zeros(9)
     for _ in range(args.steps):
         gp.push_pointers(dev_ptrs, n, on_device=True)
         st = gp.stats()
         dev_ms += st["last_push_device_ms"]
         stage += [st["last_stft_ms"], st["last_nn_ms"], st["last_istft_ms"], st["last_vadfft_ms"], st["last_scan_ms"]]
+        layer_ms += st["last_nn_layer_ms"]
+        layer_n += st["last_nn_layer_launches"]
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - t0)
     clk = clocks.stop()
@@ -282,6 +285,12 @@ def run_native(args):
         ach_tf = nn_flop / (nn_ms * 1e-3) / 1e12 if nn_ms > 0 else 0.0
         sb = frames * stft_bytes_per_frame(D, True)
         ach_gbs = sb / (stft_ms * 1e-3) / 1e9 if stft_ms > 0 else 0.0
+        # dominant kernel: one GRU layer launch (tc_gru_kernel; two layers, identical shapes).  Algorithmic flops of a
+        # launch = its share of S*n_chunks sequences x 54 steps x 2*480000 (R.h of the layer).
+        gru_ms, gru_n = layer_ms[3] + layer_ms[5], layer_n[3] + layer_n[5]
+        gru_flop_total = 2.0 * args.steps * S * n_chunks * STEPS_PER_CHUNK * 2 * 480_000
+        gru_tf = gru_flop_total / (gru_ms * 1e-3) / 1e12 if gru_ms > 0 else 0.0
+        names = fv.capi.NN_LAYERS
         out = {
             "metric": "realtime_factor_full_pipeline", "value": value, "unit": "audio-sec/sec", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "wall_ms_per_step": wall_ms / args.steps,
@@ -292,6 +301,11 @@ def run_native(args):
             "roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
                          "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,
                          "peak_source": f"{which} bf16_tflops_sustained"},
+            "kernel_roofline": {"kernel": "tc_gru_kernel (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
+                                "bound": "tensor", "achieved": gru_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": gru_tf / tf_peak,
+                                "avg_launch_ms": gru_ms / max(gru_n, 1), "flop_per_launch": gru_flop_total / max(gru_n, 1),
+                                "traffic": None, "peak_source": f"{which} bf16_tflops_sustained"},
+            "nn_layer_ms_per_step": {k: float(v) / args.steps for k, v in zip(names, layer_ms)},
             "stft_roofline": {"kernel": "stft_kernel", "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
                               "frac": ach_gbs / hbm_peak, "traffic": None, "bytes_per_frame": stft_bytes_per_frame(D, True),
                               "peak_source": f"{which} hbm_gbs"},

@@ -60,7 +60,11 @@ class BatchOptions(C.Structure):
 class BatchStats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("chunks_processed", C.c_uint64), ("vad_frames", C.c_uint64),
                 ("last_push_device_ms", C.c_double), ("last_stft_ms", C.c_double), ("last_nn_ms", C.c_double),
-                ("last_istft_ms", C.c_double), ("last_vadfft_ms", C.c_double), ("last_scan_ms", C.c_double)]
+                ("last_istft_ms", C.c_double), ("last_vadfft_ms", C.c_double), ("last_scan_ms", C.c_double),
+                ("last_nn_layer_ms", C.c_double * 9), ("last_nn_layer_launches", C.c_uint32 * 9)]
+
+
+NN_LAYERS = ("pack", "fc1", "W1", "gru1", "W2", "gru2", "fc2", "fc3", "fc4")
 
 
 NN_F32, NN_TC_F16X3, NN_TC_F16 = 0, 1, 2

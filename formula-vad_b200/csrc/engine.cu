@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <array>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace fvad {
@@ -123,7 +124,8 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
     if (opt_.device < 0 || opt_.device >= ndev) throw Error(FVAD_ERR_INVALID_ARGUMENT, "bad device ordinal");
     FVAD_CUDA_CHECK(cudaSetDevice(opt_.device));
     FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-    FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&scan_stream_, cudaStreamNonBlocking));
+    if (getenv("FVAD_SCAN_SERIAL")) scan_stream_ = stream_;  // experiments: scan on the main stream (no overlap)
+    else FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&scan_stream_, cudaStreamNonBlocking));
     FVAD_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
     for (int i = 0; i < 2; ++i) {
         FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&stage_ready_[i], cudaEventDisableTiming));
@@ -172,7 +174,7 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
 
 Batch::~Batch() {
     if (stream_) cudaStreamSynchronize(stream_);
-    if (scan_stream_) { cudaStreamSynchronize(scan_stream_); cudaStreamDestroy(scan_stream_); }
+    if (scan_stream_ && scan_stream_ != stream_) { cudaStreamSynchronize(scan_stream_); cudaStreamDestroy(scan_stream_); }
     if (scan_done_) cudaEventDestroy(scan_done_);
     if (copy_stream_) { cudaStreamSynchronize(copy_stream_); cudaStreamDestroy(copy_stream_); }
     for (int i = 0; i < 2; ++i) {
@@ -465,6 +467,7 @@ void Batch::push_any(const void *const *pcm, size_t n_pointers, size_t n, int me
                 last_ms_[1 + i] += ms;
             }
     }
+    if (nn_ && Ktot > 0) nn_->take_layer_ms(last_layer_ms_, last_layer_launches_);
     if (segment_overflow_) throw Error(FVAD_ERR_OUT_OF_MEMORY, "segment buffer overflow (more segments than max_segments)");
 }
 
@@ -524,6 +527,7 @@ void Batch::stats(fvad_batch_stats *out) const {
     out->last_push_device_ms = last_ms_[0];
     out->last_stft_ms = last_ms_[1]; out->last_nn_ms = last_ms_[2]; out->last_istft_ms = last_ms_[3];
     out->last_vadfft_ms = last_ms_[4]; out->last_scan_ms = last_ms_[5];
+    for (int i = 0; i < 9; ++i) { out->last_nn_layer_ms[i] = last_layer_ms_[i]; out->last_nn_layer_launches[i] = last_layer_launches_[i]; }
 }
 
 }  // namespace fvad

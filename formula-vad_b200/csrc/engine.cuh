@@ -108,6 +108,8 @@ private:
     // stats
     uint64_t launches0_ = 0, chunks_processed_ = 0;
     double last_ms_[6] = {};
+    double last_layer_ms_[9] = {};
+    unsigned last_layer_launches_[9] = {};
 };
 
 // eval.cu: one pair of lists (host pointers)

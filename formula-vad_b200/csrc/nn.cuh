@@ -32,6 +32,8 @@ public:
     virtual ~NnBackend() = default;
     virtual void forward(const NnSpan &span, cudaStream_t s) = 0;
     virtual const char *name() const = 0;
+    // CUDA-event ms and launch count per layer kernel {pack, fc1, W1, gru1, W2, gru2, fc2, fc3, fc4} since the last call
+    virtual void take_layer_ms(double *ms9, unsigned *launches9) { for (int i = 0; i < 9; ++i) { ms9[i] = 0; launches9[i] = 0; } }
 };
 
 std::unique_ptr<NnBackend> make_nn_f32(const HostWeights &w);

@@ -105,7 +105,6 @@ public:
         fc1_relu_ = w.fc1_relu;
         if (const char *e = getenv("FVAD_GRU_PAIR")) pair_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_NN_TIMING")) timing_ = atoi(e) != 0;
-        if (timing_) for (auto &e : tev_) FVAD_CUDA_CHECK(cudaEventCreate(&e));
         const int H = 400;
         // gate-row permutation: p = 48c + 16g + u  <-  g*400 + 16c + u
         std::vector<int> perm(3 * H);
@@ -183,34 +182,48 @@ public:
             g.out_mode = 1; g.gains = sp.gains; g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
             tc::launch_tc_gemm(g, n_sm_, s);
             mark(9, s);
-            collect(s);
+            ++batches_;
         }
     }
 
     ~NnTc() override {
-        if (!timing_) return;
-        static const char *nm[9] = {"pack", "fc1", "W1", "gru1", "W2", "gru2", "fc2", "fc3", "fc4"};
-        double tot = 0;
-        for (double v : acc_ms_) tot += v;
-        fprintf(stderr, "[fvad nn timing] total %.2f ms:", tot);
-        for (int i = 0; i < 9; ++i) fprintf(stderr, " %s %.2f (%.0f%%)", nm[i], acc_ms_[i], 100.0 * acc_ms_[i] / (tot > 0 ? tot : 1));
-        fprintf(stderr, "\n");
+        if (timing_) {
+            static const char *nm[9] = {"pack", "fc1", "W1", "gru1", "W2", "gru2", "fc2", "fc3", "fc4"};
+            double tot = 0;
+            for (double v : acc_ms_) tot += v;
+            fprintf(stderr, "[fvad nn timing] total %.2f ms:", tot);
+            for (int i = 0; i < 9; ++i) fprintf(stderr, " %s %.2f (%.0f%%)", nm[i], acc_ms_[i], 100.0 * acc_ms_[i] / (tot > 0 ? tot : 1));
+            fprintf(stderr, "\n");
+        }
         for (auto &e : tev_) cudaEventDestroy(e);
+    }
+
+    // per-layer CUDA-event time and launch counts since the last call (the caller has synchronised the stream)
+    void take_layer_ms(double *ms9, unsigned *launches9) override {
+        static const int per_batch[9] = {1, 1, 1, 1, 1, 1, 1, 1, 1};
+        for (int i = 0; i < 9; ++i) { ms9[i] = 0; launches9[i] = 0; }
+        for (size_t b = 0; b < batches_; ++b)
+            for (int i = 0; i < 9; ++i) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, tev_[b * 10 + i], tev_[b * 10 + i + 1]);
+                ms9[i] += ms; acc_ms_[i] += ms; launches9[i] += per_batch[i];
+            }
+        batches_ = 0;
     }
 
 private:
     int n_sm_ = 148, fc1_relu_ = 0;
     Layer fc1_, gW_[2], fc2_, fc3_, fc4_;
     DevBuf<__half> gR_[2], gR2_[2];
-    // FVAD_NN_TIMING=1: CUDA-event time per layer kernel, summed over the handle's lifetime (adds a sync per sub-batch)
+    // per-layer CUDA-event timing (events only, no extra synchronisation); FVAD_NN_TIMING=1 prints the lifetime sums
     bool timing_ = false;
-    cudaEvent_t tev_[10] = {};
+    std::vector<cudaEvent_t> tev_;   // 10 per sub-batch of the current push
+    size_t batches_ = 0;
     double acc_ms_[9] = {};
-    void mark(int i, cudaStream_t s) { if (timing_) cudaEventRecord(tev_[i], s); }
-    void collect(cudaStream_t s) {
-        if (!timing_) return;
-        cudaStreamSynchronize(s);
-        for (int i = 0; i < 9; ++i) { float ms = 0; cudaEventElapsedTime(&ms, tev_[i], tev_[i + 1]); acc_ms_[i] += ms; }
+    void mark(int i, cudaStream_t s) {
+        const size_t k = batches_ * 10 + (size_t)i;
+        while (tev_.size() <= k) { cudaEvent_t e; FVAD_CUDA_CHECK(cudaEventCreate(&e)); tev_.push_back(e); }
+        cudaEventRecord(tev_[k], s);
     }
     DevBuf<unsigned long long> trace_;
     bool traced_ = false;
@@ -239,6 +252,7 @@ private:
         g.A = A; g.B = L.img.p; g.bias = L.bias.p; g.C = C;
         g.K = L.K; g.Nc = L.Nc; g.n_valid = L.n_valid; g.n_tiles = L.n_tiles;
         for (int j = 0; j < L.n_tiles; ++j) { g.nt_size[j] = L.nt_size[j]; g.nt_col[j] = L.nt_col[j]; g.nt_off[j] = L.nt_off[j]; }
+        if (const char *e = getenv("FVAD_GEMM_DBG")) g.dbg = atoi(e);
         g.mt_count = Q * T; g.T = T; g.A_q = A_q; g.A_t0 = A_t0; g.C_q = C_q; g.C_t0 = C_t0; g.act = act;
         return g;
     }

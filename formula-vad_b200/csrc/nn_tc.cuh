@@ -35,6 +35,7 @@ struct GemmArgs {
     int mt_count, T, A_q, A_t0, C_q, C_t0;
     int act;       // 0 none, 1 relu, 2 sigmoid
     int out_mode;
+    int dbg;       // experiments only (FVAD_GEMM_DBG): bit 0 epilogue does no work, bit 1 producer copies nothing
     int seq0, n_seq, Kchunks;  // scatter: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
 };
 void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s);

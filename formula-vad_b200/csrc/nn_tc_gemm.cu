@@ -21,10 +21,14 @@ namespace {
 // The A tile of an M-tile is fetched once (through the same producer queue, slab by slab, while the
 // first N-tile runs) and stays resident for all N-tiles, so L2 traffic per M-tile is A + the whole
 // weight matrix: 128 flop per byte, the same intensity as the GRU kernel's R stream.
-constexpr int kMaxSlabs = 20;
+constexpr int kMaxSlabs = 40;
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 256;
-constexpr int kSmemTotal = 227 * 1024;
+// 214 KB, not the full 227: the VAD scan of the previous span runs concurrently on its own stream (one warp and
+// ~11 KB of shared memory per stream); a persistent GEMM CTA that takes a whole SM's shared memory cannot start
+// on the SMs the scan occupies, and with a static tile assignment the late CTAs stretch the kernel by ~60 %
+// (measured: W1, which overlaps the scan, 12.3 ms vs W2 7.6 ms for the same GEMM).
+constexpr int kSmemTotal = 214 * 1024;
 
 struct GemmShared {
     uint64_t full[kMaxStages], empty[kMaxStages], a_full[kMaxSlabs], a_empty[kMaxSlabs], acc_full[2], acc_empty[2];
@@ -89,8 +93,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                         }
                         mbar_wait(&sh->empty[st], ph ^ 1);
                         const uint32_t bb = (uint32_t)(kw / 8) * (NT * 16);
-                        mbar_expect_tx(&sh->full[st], bb);
-                        bulk_g2s(sB + (size_t)st * pl.stage_bytes, Bt + (size_t)(k0 / 8) * (NT * 16), bb, &sh->full[st]);
+                        if (a.dbg & 2) { mbar_arrive(&sh->full[st]); }
+                        else {
+                            mbar_expect_tx(&sh->full[st], bb);
+                            bulk_g2s(sB + (size_t)st * pl.stage_bytes, Bt + (size_t)(k0 / 8) * (NT * 16), bb, &sh->full[st]);
+                        }
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                 }
@@ -176,7 +183,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                 mbar_wait(&sh->acc_full[buf], (work >> 1) & 1);
                 tc_fence_after();
                 const uint32_t tbase = tmem + buf * 256 + ((uint32_t)(wq * 32) << 16);
-                for (int c = 0; c < NT; c += 32) {
+                for (int c = 0; c < ((a.dbg & 1) ? 0 : NT); c += 32) {
                     uint32_t r[32];
                     const bool full32 = c + 32 <= NT;  // N-tiles are multiples of 16
                     if (full32) {

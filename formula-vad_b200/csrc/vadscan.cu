@@ -252,6 +252,16 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
 void launch_vadscan(const ScanArgs &a, cudaStream_t s) {
     if (a.n_frames <= 0) return;
     const int total = a.S * a.M;
+    static bool attr = false;
+    if (!attr) {
+        // The scan runs on its own stream next to the persistent NSNet2 kernels of the following span, which need
+        // ~200 KB of shared memory per SM.  An SM whose L1/shared split was set up for this small kernel cannot take
+        // one of their CTAs until the scan's CTA leaves (measured: +35 % on the overlapped GRU launch), so ask for
+        // the maximum shared-memory carveout here and the two kinds of CTA share an SM.
+        cudaFuncSetAttribute(vadscan_warp_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(vadscan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr = true;
+    }
     if (a.fast) vadscan_warp_kernel<<<(unsigned)total, kScanThreads, 0, s>>>(a);
     else vadscan_kernel<<<(unsigned)((total + kScanThreads - 1) / kScanThreads), kScanThreads, 0, s>>>(a);
     FVAD_LAUNCHED();

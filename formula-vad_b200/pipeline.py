@@ -344,7 +344,7 @@ class BatchPipeline:
     def stats(self) -> dict:
         st = capi.BatchStats()
         check(self._L.fvad_batch_stats_get(self._h, C.byref(st)))
-        return {k: getattr(st, k) for k, _ in capi.BatchStats._fields_}
+        return {k: (list(getattr(st, k)) if k.startswith("last_nn_layer") else getattr(st, k)) for k, _ in capi.BatchStats._fields_}
 
     def close(self):
         if self._h:

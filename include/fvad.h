@@ -182,6 +182,9 @@ typedef struct fvad_batch_stats {
     uint64_t vad_frames;       /* per stream */
     double last_push_device_ms;/* CUDA-event time of the last push, H2D/D2H included when host memory */
     double last_stft_ms, last_nn_ms, last_istft_ms, last_vadfft_ms, last_scan_ms; /* per-stage CUDA-event time, summed over the spans of the last push */
+    /* NSNet2 per layer kernel {pack, fc1, W1, gru1, W2, gru2, fc2, fc3, fc4}: CUDA-event time and launches of the last push */
+    double last_nn_layer_ms[9];
+    uint32_t last_nn_layer_launches[9];
 } fvad_batch_stats;
 
 typedef enum fvad_tap {
