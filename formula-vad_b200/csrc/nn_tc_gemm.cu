@@ -263,7 +263,7 @@ void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     for (;;) {
         pl.stage_bytes = nt_max * pl.KS * 2;
         pl.n_stages = (kSmemTotal - pl.a_bytes - fixed) / pl.stage_bytes;
-        if (pl.n_stages >= 4 || pl.KS == 16) break;
+        if (pl.n_stages >= 3 || pl.KS == 16) break;  // fewer, larger stages: the per-stage barrier round trip costs the issuing thread more than the shorter ring
         pl.KS /= 2;
     }
     if (pl.n_stages > kMaxStages) pl.n_stages = kMaxStages;
