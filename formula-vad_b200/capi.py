@@ -85,6 +85,18 @@ EXPORTS = (
 )
 
 
+class Recording(C.Structure):  # fvad_recording (AudioBuffer handed to AudioPipeline.Callbacks)
+    _fields_ = [("n_channels", C.c_size_t), ("length", C.c_size_t), ("sample_rate", C.c_size_t),
+                ("global_start_frame_number", C.c_uint64), ("channel_pcm", C.POINTER(C.POINTER(C.c_float)))]
+
+
+RECORDING_CB = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(Recording))
+
+
+class Callbacks(C.Structure):  # fvad_callbacks
+    _fields_ = [("ctx", C.c_void_p), ("on_original_recording", RECORDING_CB), ("on_denoised_recording", RECORDING_CB)]
+
+
 class EvalSegment(C.Structure):  # fvad_eval_segment
     _fields_ = [("from_sec", C.c_float), ("to_sec", C.c_float)]
 

@@ -1,5 +1,6 @@
 // capi.cu -- the extern "C" surface declared in include/fvad.h.  Exceptions never cross it.
 #include <cmath>
+#include <algorithm>
 #include <cstring>
 #include <new>
 
@@ -47,11 +48,88 @@ struct fvad_fft {
 struct fvad_batch {
     Batch *impl = nullptr;
 };
+// Recording extraction for the pipeline facade: what AudioPipeline.startRecording / endRecording and the two
+// MRBRecorders deliver (reference src/AudioPipeline.zig:181-209, AudioPipeline/MRBRecorder.zig:76-203): for every
+// VAD segment of the main machine, the original and the denoised PCM [sample_from, sample_to) as planar f32,
+// handed to the callbacks once the samples exist (sample_to lies 2 s past the speech end, so usually a later push
+// completes it).  The reference copies out of its 10 s rings while a recording is in progress; here the facade keeps
+// a host-side history that is trimmed to what a current or future recording can still reach.
+struct RecHistory {
+    std::vector<std::vector<float>> ch;
+    uint64_t base = 0;  // absolute sample index of ch[c][0]
+    uint64_t end() const { return base + (ch.empty() ? 0 : ch[0].size()); }
+    void append(size_t c, const float *src, size_t n) { ch[c].insert(ch[c].end(), src, src + n); }
+    void trim(uint64_t keep_from) {
+        if (keep_from <= base) return;
+        const size_t drop = (size_t)std::min<uint64_t>(keep_from - base, ch.empty() ? 0 : ch[0].size());
+        for (auto &v : ch) v.erase(v.begin(), v.begin() + (long)drop);
+        base += drop;
+    }
+};
+struct PendingRec {
+    uint64_t from, to;
+    bool orig_done, den_done;
+};
 struct fvad_pipeline {
     Batch *impl = nullptr;
     fvad_callbacks cb{};
     bool has_cb = false;
+    size_t sample_rate = 0, n_channels = 0, seg_seen = 0;
+    RecHistory orig, den;
+    std::vector<PendingRec> pending;
+    std::vector<float> tapbuf;
 };
+
+static void deliver(const fvad_pipeline *p, const RecHistory &h, const PendingRec &r, bool denoised) {
+    auto fn = denoised ? p->cb.on_denoised_recording : p->cb.on_original_recording;
+    if (!fn) return;
+    const uint64_t from = std::max(r.from, h.base);
+    std::vector<const float *> ptrs(p->n_channels);
+    for (size_t c = 0; c < p->n_channels; ++c) ptrs[c] = h.ch[c].data() + (from - h.base);
+    fvad_recording rec;
+    rec.n_channels = p->n_channels;
+    rec.length = (size_t)(r.to - from);
+    rec.sample_rate = p->sample_rate;
+    rec.global_start_frame_number = from;
+    rec.channel_pcm = ptrs.data();
+    fn(p->cb.ctx, &rec);  // borrowed for the call, like the reference's AudioBuffer (AudioPipeline.zig:193-199)
+}
+
+static void run_recorders(fvad_pipeline *p, const float *const *pcm, size_t n) {
+    const size_t C = p->n_channels;
+    for (size_t c = 0; c < C; ++c) p->orig.append(c, pcm[c], n);
+    // denoised samples of the chunks this push completed
+    const size_t n_el = p->impl->tap(FVAD_TAP_DENOISED, nullptr, 0);
+    if (n_el) {
+        p->tapbuf.resize(n_el);
+        p->impl->tap(FVAD_TAP_DENOISED, p->tapbuf.data(), n_el * sizeof(float));
+        const size_t per = n_el / C;
+        for (size_t c = 0; c < C; ++c) p->den.append(c, p->tapbuf.data() + c * per, per);
+    }
+    const fvad_segment *segs = nullptr;
+    size_t n_seg = 0;
+    p->impl->segments(0, 0, &segs, &n_seg);
+    for (; p->seg_seen < n_seg; ++p->seg_seen)
+        p->pending.push_back(PendingRec{segs[p->seg_seen].sample_from, segs[p->seg_seen].sample_to, false, false});
+    for (auto &r : p->pending) {
+        if (!r.orig_done && r.to <= p->orig.end()) { deliver(p, p->orig, r, false); r.orig_done = true; }
+        if (!r.den_done && r.to <= p->den.end()) { deliver(p, p->den, r, true); r.den_done = true; }
+    }
+    p->pending.erase(std::remove_if(p->pending.begin(), p->pending.end(), [](const PendingRec &r) { return r.orig_done && r.den_done; }),
+                     p->pending.end());
+    // retention: unfinished recordings, a speech run in progress (its recording starts 2 s before it), and the 2 s
+    // a run that starts in not-yet-processed audio can reach back
+    const uint64_t margin = (uint64_t)((float)p->sample_rate * 2);
+    uint64_t keep = p->impl->processed_samples();
+    keep = keep > margin + 1024 ? keep - margin - 1024 : 0;
+    int state = 0;
+    uint64_t start = 0;
+    p->impl->machine_state(0, 0, &state, &start);
+    if (state != 0) keep = std::min(keep, start > margin ? start - margin : 0);
+    for (const auto &r : p->pending) keep = std::min(keep, r.from);
+    p->orig.trim(keep);
+    p->den.trim(keep);
+}
 struct fvad_nsnet2 {
     Batch *impl = nullptr;
     size_t sample_rate = 0;
@@ -332,8 +410,12 @@ int fvad_pipeline_create_with_weights(const fvad_config *cfg, const fvad_callbac
         fvad_batch_options_default(&opt);
         opt.nn_mode = nn_mode;
         auto *p = new fvad_pipeline;
+        if (cb && (cb->on_original_recording || cb->on_denoised_recording)) { p->cb = *cb; p->has_cb = true; opt.keep_taps = 1; }
         try { p->impl = make_batch(1, *cfg, w, opt); } catch (...) { delete p; throw; }
-        if (cb) { p->cb = *cb; p->has_cb = true; }
+        p->sample_rate = cfg->sample_rate;
+        p->n_channels = cfg->n_channels;
+        p->orig.ch.resize(cfg->n_channels);
+        p->den.ch.resize(cfg->n_channels);
         *out = p;
     });
 }
@@ -353,6 +435,7 @@ int fvad_pipeline_push_samples(fvad_pipeline *p, const float *const *pcm, size_t
         if (!p) throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL handle");
         if (first) *first = p->impl->total_write_count();  // AudioPipeline.zig:119
         p->impl->push(pcm, n_channels, n, 0);
+        if (p->has_cb && !p->impl->skipping()) run_recorders(p, pcm, n);
     });
 }
 

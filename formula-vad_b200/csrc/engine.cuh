@@ -37,6 +37,14 @@ public:
     // eval.cu: statistics of every (stream, machine) list against the streams' reference segments; out [S][M]
     void evaluate(const fvad_eval_segment *refs, const size_t *ref_offsets, const fvad_eval_config &cfg, fvad_eval_stats *out);
     uint64_t total_write_count() const { return total_written_; }
+    bool skipping() const { return skip_; }
+    uint64_t processed_samples() const { return processed_; }   // per channel, whole chunks
+    // FSM state (0 closed, 1 opening, 2 open, 3 closing) and speech_start_index of a machine after the last push
+    void machine_state(size_t stream, size_t machine, int *state, uint64_t *start_index) const {
+        const ScanState &st = h_states_[stream * (size_t)M_ + machine];
+        if (state) *state = st.state;
+        if (start_index) *start_index = st.start_index;
+    }
     size_t n_machines() const { return (size_t)M_; }
     size_t n_streams() const { return (size_t)S_; }
     size_t n_channels() const { return (size_t)C_; }

@@ -180,18 +180,32 @@ class AudioPipeline:
 
     def __init__(self, sample_rate: int, n_channels: int, weights: dict | None = None, vad_machine_config=None,
                  alt_vad_machine_configs=None, denoiser_model_path: str | None = None, skip_processing=False,
-                 nn_mode: int = capi.NN_F32, fft_size: int = 1024):
+                 nn_mode: int = capi.NN_F32, fft_size: int = 1024, on_original_recording=None,
+                 on_denoised_recording=None):
+        """on_*_recording(start_index, pcm[channels][n], sample_rate): AudioPipeline.Callbacks (AudioPipeline.zig:14-18);
+        the arrays are copies (the C buffers are only borrowed for the call)."""
         self._L = capi.lib()
         self.cfg, self._keep = _config(sample_rate, n_channels, vad_machine_config, alt_vad_machine_configs,
                                        denoiser_model_path, skip_processing, fft_size)
         self.n_channels = n_channels
+        cbp = None
+        if on_original_recording or on_denoised_recording:
+            def wrap(fn):
+                def thunk(_ctx, rec):
+                    r = rec.contents
+                    pcm = np.stack([np.ctypeslib.as_array(r.channel_pcm[c], shape=(r.length,)).copy() for c in range(r.n_channels)])
+                    fn(int(r.global_start_frame_number), pcm, int(r.sample_rate))
+                return capi.RECORDING_CB(thunk) if fn else capi.RECORDING_CB()
+            cbs = capi.Callbacks(None, wrap(on_original_recording), wrap(on_denoised_recording))
+            self._keep.append(cbs)
+            cbp = C.byref(cbs)
         h = C.c_void_p()
         if weights is not None:
             w, k = capi.make_weights(weights)
             self._keep.append(k)
-            check(self._L.fvad_pipeline_create_with_weights(C.byref(self.cfg), None, C.byref(w), nn_mode, C.byref(h)))
+            check(self._L.fvad_pipeline_create_with_weights(C.byref(self.cfg), cbp, C.byref(w), nn_mode, C.byref(h)))
         else:
-            check(self._L.fvad_pipeline_create(C.byref(self.cfg), None, C.byref(h)))
+            check(self._L.fvad_pipeline_create(C.byref(self.cfg), cbp, C.byref(h)))
         self._h = h
 
     def push_samples(self, channel_pcm) -> int:

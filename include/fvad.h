@@ -125,7 +125,10 @@ FVAD_API int fvad_nsnet2_calc_spectrogram(const float *audio_chunk, size_t n_aud
 
 /* ------------------------------------------------------------------------------------------
  * Pipeline facade -- replaces src/AudioPipeline.zig (+ AudioPipeline/VADPipeline.zig and the
- * steps it drives).  Recording callbacks (MRBRecorder) are SURVEY 8(f) "next".
+ * steps it drives).  Recording callbacks: for every VAD segment of the main machine the original and the
+ * denoised PCM [sample_from, sample_to) are handed to the callbacks once those samples exist -- what
+ * startRecording / endRecording and the two MRBRecorders deliver (AudioPipeline.zig:181-209,
+ * AudioPipeline/MRBRecorder.zig:76-203).
  * ---------------------------------------------------------------------------------------- */
 typedef struct fvad_pipeline fvad_pipeline;
 

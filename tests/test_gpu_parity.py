@@ -255,3 +255,33 @@ def test_double_buffered_host_ingest_and_int16(fv, wd):
             assert np.array_equal(np.concatenate(gains, axis=1), r_gain), (i16, cuts)
             assert [gp.segments(s) for s in range(S)] == r_segs
             gp.close()
+
+
+def test_recording_callbacks_deliver_segment_audio(fv, wd):
+    """AudioPipeline.Callbacks (AudioPipeline.zig:14-18,181-209): every VAD segment of the main machine is handed
+    over as original and denoised planar PCM [sample_from, sample_to), once the samples exist, across pushes."""
+    sr, nch = 16000, 2
+    x, _ = fv.synth.onboard_stream(77, 70.0, sr, nch)
+    x = np.concatenate([x, np.zeros((nch, 6 * sr), np.float32)], axis=1)  # trailing audio so the 2 s end margin exists
+    ref = fv.BatchPipeline(1, sr, nch, wd, keep_taps=True)
+    ref.push(x)
+    den = ref.tap(fv.capi.TAP_DENOISED)
+    segs = ref.segments(0)
+    ref.close()
+    assert len(segs) >= 1
+    got = {"orig": [], "den": []}
+    p = fv.AudioPipeline(sr, nch, weights=wd,
+                         on_original_recording=lambda i, pcm, r: got["orig"].append((i, pcm, r)),
+                         on_denoised_recording=lambda i, pcm, r: got["den"].append((i, pcm, r)))
+    step = sr  # one-second pushes, like the reference's file reader (SimulationInstance.zig:183-213)
+    for a in range(0, x.shape[1], step):
+        p.push_samples(list(x[:, a:a + step]))
+    assert p.vad_segments() == segs
+    done = [s for s in segs if s[1] <= den.shape[1]]
+    assert len(done) >= 1 and len(got["orig"]) == len(done) and len(got["den"]) == len(done)
+    for (f, t, _, _), (io, po_, ro), (idn, pd, rd) in zip(done, got["orig"], got["den"]):
+        assert io == f and idn == f and ro == sr and rd == sr
+        assert po_.shape == (nch, t - f) and pd.shape == (nch, t - f)
+        assert np.array_equal(po_, x[:, f:t])
+        assert np.array_equal(pd, den[:, f:t])
+    p.deinit()
