@@ -219,6 +219,7 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
     sa.halo_in = halo_[parity_].p; sa.halo_out = halo_[parity_ ^ 1].p;
     sa.spec = spec_.p; sa.feat = feat_.p; sa.sumsq = sumsq_.p;
     sa.K = K; sa.SC = SC_; sa.D = D_;
+    sa.nn_tiles = (nn_ && full && !forced_.p) ? nn_->input_tiles(SC_, K) : nullptr;
     launch_stft(sa, tables_, s);
     // 4 context feature rows carried from the previous span (NSNet2.zig:188-203)
     launch_copy_rows(feat_.p, ctx_carry_.p, frow * kBins, (size_t)kCtx * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
@@ -234,7 +235,7 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
             if (f0 + rows > opt_.forced_gain_frames) throw Error(FVAD_ERR_INVALID_ARGUMENT, "forced_gains shorter than the audio");
             launch_copy_rows(gains_.p, forced_.p + f0 * kBins, rows * kBins, opt_.forced_gain_frames * kBins, rows * kBins, (size_t)SC_, s);
         } else {
-            NnSpan ns{feat_.p, gains_.p, SC_, K};
+            NnSpan ns{feat_.p, gains_.p, SC_, K, ctx_carry_.p, sa.nn_tiles != nullptr};
             nn_->forward(ns, s);
         }
         FVAD_CUDA_CHECK(cudaEventRecord(ev_[2], s));

@@ -25,6 +25,8 @@ struct NnSpan {
     const float *feat;  // [SC][4+50K][161]
     float *gains;       // [SC][50K][161]
     int SC, K;
+    const float *ctx;   // [SC][4][161] context rows of each stream-channel's first chunk (only read when tiles_ready)
+    bool tiles_ready;   // the STFT already wrote the backend's input tiles (input_tiles()) for rows it owns
 };
 
 class NnBackend {
@@ -32,6 +34,9 @@ public:
     virtual ~NnBackend() = default;
     virtual void forward(const NnSpan &span, cudaStream_t s) = 0;
     virtual const char *name() const = 0;
+    // tensor-core backend: device buffer the STFT may fill directly with fp16 input tiles for a span of SC x K
+    // sequences (nullptr: the backend reads the f32 feature rows itself)
+    virtual void *input_tiles(int SC, int K) { (void)SC; (void)K; return nullptr; }
     // CUDA-event ms and launch count per layer kernel {pack, fc1, W1, gru1, W2, gru2, fc2, fc3, fc4} since the last call
     virtual void take_layer_ms(double *ms9, unsigned *launches9) { for (int i = 0; i < 9; ++i) { ms9[i] = 0; launches9[i] = 0; } }
 };

@@ -18,32 +18,50 @@ namespace tc {
 
 // ---- pack kernel: features f32 -> fp16 tiles -------------------------------------------------
 __global__ void __launch_bounds__(256) tc_pack_kernel(const PackArgs a) {
-    // one CTA per (q, t) tile: 128 rows x 176 columns
+    // one CTA per (q, t) tile: 128 rows x 176 columns.  A warp reads whole feature rows (161 consecutive floats,
+    // coalesced) and drops them as halves into a shared-memory image of the tile; the image then leaves with
+    // 16-byte stores in tile order, so both directions move full sectors.
+    __shared__ __align__(16) uint8_t img[kTileM * 176 * 2];
     const int q = blockIdx.x / kSteps, t = blockIdx.x % kSteps;
-    uint8_t *tile = reinterpret_cast<uint8_t *>(a.A0) + (size_t)blockIdx.x * tile_bytes(176);
-    // thread -> (row, core-column): 128 rows x 22 core-columns, 16 B each
-    for (int i = threadIdx.x; i < kTileM * 22; i += blockDim.x) {
-        const int row = i % kTileM, cc = i / kTileM;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int row = warp; row < kTileM; row += 8) {
         const int g = a.seq0 + q * kTileM + row;
-        uint4 out = make_uint4(0, 0, 0, 0);
-        if (g < a.n_seq) {
-            const int sc = g / a.Kchunks, j = g % a.Kchunks;
-            const float *src = a.feat + ((size_t)sc * (kCtx + kFrames * a.Kchunks) + (size_t)kFrames * j + t) * kBins + cc * 8;
-            float v[8];
+        const bool ok = g < a.n_seq;
+        const int sc = ok ? g / a.Kchunks : 0, j = ok ? g % a.Kchunks : 0;
+        const float *src = a.feat + ((size_t)sc * (kCtx + kFrames * a.Kchunks) + (size_t)kFrames * j + t) * kBins;
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = (cc * 8 + e < kBins) ? __ldg(src + e) : 0.0f;
-            __half2 h0 = __floats2half2_rn(v[0], v[1]), h1 = __floats2half2_rn(v[2], v[3]);
-            __half2 h2 = __floats2half2_rn(v[4], v[5]), h3 = __floats2half2_rn(v[6], v[7]);
-            out.x = *reinterpret_cast<uint32_t *>(&h0); out.y = *reinterpret_cast<uint32_t *>(&h1);
-            out.z = *reinterpret_cast<uint32_t *>(&h2); out.w = *reinterpret_cast<uint32_t *>(&h3);
+        for (int i = 0; i < 6; ++i) {
+            const int k = lane + 32 * i;
+            if (k < 176) {
+                const float v = (ok && k < kBins) ? __ldg(src + k) : 0.0f;
+                *reinterpret_cast<__half *>(img + tiled_off(row, k, kTileM)) = __float2half_rn(v);
+            }
         }
-        *reinterpret_cast<uint4 *>(tile + (size_t)cc * (kTileM * 16) + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16) = out;
     }
+    __syncthreads();
+    uint4 *dst = reinterpret_cast<uint4 *>(reinterpret_cast<uint8_t *>(a.A0) + (size_t)blockIdx.x * tile_bytes(176));
+    const uint4 *srcv = reinterpret_cast<const uint4 *>(img);
+    for (int i = threadIdx.x; i < kTileM * 176 * 2 / 16; i += 256) dst[i] = srcv[i];
 }
 
 void launch_tc_pack(const PackArgs &a, cudaStream_t s) {
     if (a.Q <= 0) return;
     tc_pack_kernel<<<(unsigned)(a.Q * kSteps), 256, 0, s>>>(a);
+    FVAD_LAUNCHED();
+    FVAD_CUDA_CHECK(cudaGetLastError());
+}
+
+// context rows t = 0..3 of every stream-channel's first sequence of the span (f32 carry [SC][4][161] -> tiles)
+__global__ void tc_ctx_pack_kernel(const float *ctx, __half *A0, int SC, int K) {
+    const int sc = blockIdx.x / kCtx, t = blockIdx.x % kCtx;
+    const int g = sc * K;
+    uint8_t *tile = reinterpret_cast<uint8_t *>(A0) + ((size_t)(g >> 7) * kSteps + t) * tile_bytes(176);
+    for (int k = threadIdx.x; k < kBins; k += blockDim.x)
+        *reinterpret_cast<__half *>(tile + tiled_off(g & 127, k, kTileM)) = __float2half_rn(ctx[((size_t)sc * kCtx + t) * kBins + k]);
+}
+
+void launch_tc_ctx_pack(const float *ctx, __half *A0, int SC, int K, cudaStream_t s) {
+    tc_ctx_pack_kernel<<<(unsigned)(SC * kCtx), 192, 0, s>>>(ctx, A0, SC, K);
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
 }
@@ -55,7 +73,7 @@ namespace {
 using tc::GemmArgs;
 
 struct Layer {  // one dense layer prepared for launch_tc_gemm
-    DevBuf<__half> img;
+    DevBuf<__half> img, img2;
     DevBuf<float> bias;
     int K = 0, Nc = 0, n_valid = 0, n_tiles = 0;
     int nt_size[tc::kMaxNTiles] = {}, nt_col[tc::kMaxNTiles] = {};
@@ -89,6 +107,22 @@ void build_layer(Layer &L, const float *W, const float *bias, const int *perm, i
     }
     L.img.ensure(img.size());
     FVAD_CUDA_CHECK(cudaMemcpy(L.img.p, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    // CTA-pair image: same N-tile offsets, each tile split into two halves of NT/2 rows tiled with R = NT/2
+    std::vector<__half> img2(off / 2, __float2half(0.0f));
+    for (size_t j = 0; j < tiles.size(); ++j) {
+        const int NT = tiles[j], NH = NT / 2;
+        uint8_t *base = reinterpret_cast<uint8_t *>(img2.data()) + L.nt_off[j];
+        for (int n = 0; n < NT; ++n) {
+            const int p = L.nt_col[j] + n;
+            if (p >= n_valid) continue;
+            const int src = perm ? perm[p] : p;
+            uint8_t *hb = base + (size_t)(n / NH) * NH * Kp * 2;
+            for (int k = 0; k < Kin; ++k)
+                *reinterpret_cast<__half *>(hb + tc::tiled_off(n % NH, k, NH)) = __float2half_rn(W[(size_t)src * Kin + k]);
+        }
+    }
+    L.img2.ensure(img2.size());
+    FVAD_CUDA_CHECK(cudaMemcpy(L.img2.p, img2.data(), img2.size() * sizeof(__half), cudaMemcpyHostToDevice));
     L.bias.ensure(b.size());
     FVAD_CUDA_CHECK(cudaMemcpy(L.bias.p, b.data(), b.size() * sizeof(float), cudaMemcpyHostToDevice));
 }
@@ -105,6 +139,8 @@ public:
         fc1_relu_ = w.fc1_relu;
         if (const char *e = getenv("FVAD_GRU_PAIR")) pair_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_NN_TIMING")) timing_ = atoi(e) != 0;
+        if (const char *e = getenv("FVAD_GEMM_PAIR")) gemm_pair_ = atoi(e) != 0;
+        if (const char *e = getenv("FVAD_FUSED_PACK")) fused_pack_ = atoi(e) != 0;
         const int H = 400;
         // gate-row permutation: p = 48c + 16g + u  <-  g*400 + 16c + u
         std::vector<int> perm(3 * H);
@@ -147,11 +183,24 @@ public:
     }
     const char *name() const override { return "tcgen05-f16"; }
 
+    // the STFT writes the fp16 input tiles of a whole span itself (fused pack); pad rows/columns stay zero
+    void *input_tiles(int SC, int K) override {
+        if (!fused_pack_) return nullptr;
+        const size_t q_total = ((size_t)SC * K + tc::kTileM - 1) / tc::kTileM;
+        const size_t need = q_total * kSteps * tc::tile_bytes(176) / 2;
+        if (need > a0_.n) {
+            a0_.ensure(need);
+            FVAD_CUDA_CHECK(cudaMemset(a0_.p, 0, a0_.n * sizeof(__half)));
+        }
+        return a0_.p;
+    }
+
     void forward(const NnSpan &sp, cudaStream_t s) override {
         const int total = sp.SC * sp.K;
         const int q_total = (total + tc::kTileM - 1) / tc::kTileM;
         const int QB = std::min(q_total, 2 * n_sm_);  // tiles per sub-batch
-        a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
+        if (!sp.tiles_ready) a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
+        else tc::launch_tc_ctx_pack(sp.ctx, a0_.p, sp.SC, sp.K, s);
         x1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
         xp_.ensure((size_t)QB * kSteps * tc::tile_bytes(1200) / 2);
         h1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
@@ -160,12 +209,28 @@ public:
         f3_.ensure((size_t)QB * kFrames * tc::tile_bytes(608) / 2);
         for (int q0 = 0; q0 < q_total; q0 += QB) {
             const int Q = std::min(QB, q_total - q0);
+            const __half *a0 = sp.tiles_ready ? a0_.p + (size_t)q0 * kSteps * tc::tile_bytes(176) / 2 : a0_.p;
             tc::PackArgs pa{sp.feat, a0_.p, Q, q0 * tc::kTileM, total, sp.K};
             mark(0, s);
-            tc::launch_tc_pack(pa, s);
+            if (!sp.tiles_ready) tc::launch_tc_pack(pa, s);
             mark(1, s);
-            gemm(fc1_, a0_.p, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
+            gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
             mark(2, s);
+            if (const char *tp = getenv("FVAD_GEMM_TRACE")) {
+                if (!gtraced_) {  // debug only: CTA 0's timeline of the first W1 launch
+                    gtraced_ = true;
+                    const size_t ne = 5 * 4 * 8 * 32;
+                    gtrace_.ensure(ne);
+                    FVAD_CUDA_CHECK(cudaMemsetAsync(gtrace_.p, 0, ne * 8, s));
+                    GemmArgs g = base_args(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0);
+                    g.trace = gtrace_.p;
+                    tc::launch_tc_gemm(g, n_sm_, s);
+                    std::vector<unsigned long long> h(ne);
+                    FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
+                    FVAD_CUDA_CHECK(cudaMemcpy(h.data(), gtrace_.p, ne * 8, cudaMemcpyDeviceToHost));
+                    if (FILE *f = fopen(tp, "wb")) { fwrite(h.data(), 8, ne, f); fclose(f); }
+                }
+            }
             gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             mark(3, s);
             gru(0, h1_.p, Q, 0, s);
@@ -180,7 +245,7 @@ public:
             mark(8, s);
             GemmArgs g = base_args(fc4_, f3_.p, nullptr, Q, kFrames, kFrames, 0, kFrames, 0, 2);
             g.out_mode = 1; g.gains = sp.gains; g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
-            tc::launch_tc_gemm(g, n_sm_, s);
+            launch(g, s);
             mark(9, s);
             ++batches_;
         }
@@ -225,9 +290,13 @@ private:
         while (tev_.size() <= k) { cudaEvent_t e; FVAD_CUDA_CHECK(cudaEventCreate(&e)); tev_.push_back(e); }
         cudaEventRecord(tev_[k], s);
     }
-    DevBuf<unsigned long long> trace_;
+    DevBuf<unsigned long long> trace_, gtrace_;
+    bool gtraced_ = false;
     bool traced_ = false;
-    bool pair_ = false;  // CTA-pair GRU (FVAD_GRU_PAIR=0 selects the one-CTA kernel, kept for A/B measurements)
+    bool pair_ = false;
+    bool fused_pack_ = false;  // FVAD_FUSED_PACK=1: the STFT writes the fp16 input tiles itself -- measured slower (its 16-byte
+                               // pieces land 2 KB apart and cost the STFT +75 %, more than the pack kernel's 5 ms), kept for A/B
+    bool gemm_pair_ = false;  // CTA-pair GEMM (FVAD_GEMM_PAIR=1): parity-green but 50 % slower than the one-CTA kernel, kept for A/B
 
     void gru(int l, __half *hout, int Q, int t_store_min, cudaStream_t s) {
         unsigned long long *tr = nullptr;
@@ -249,15 +318,19 @@ private:
     static GemmArgs base_args(const Layer &L, const __half *A, __half *C, int Q, int T, int A_q, int A_t0, int C_q, int C_t0, int act) {
         GemmArgs g;
         memset(&g, 0, sizeof(g));
-        g.A = A; g.B = L.img.p; g.bias = L.bias.p; g.C = C;
+        g.A = A; g.B = L.img.p; g.B2 = L.img2.p; g.bias = L.bias.p; g.C = C;
         g.K = L.K; g.Nc = L.Nc; g.n_valid = L.n_valid; g.n_tiles = L.n_tiles;
         for (int j = 0; j < L.n_tiles; ++j) { g.nt_size[j] = L.nt_size[j]; g.nt_col[j] = L.nt_col[j]; g.nt_off[j] = L.nt_off[j]; }
         if (const char *e = getenv("FVAD_GEMM_DBG")) g.dbg = atoi(e);
         g.mt_count = Q * T; g.T = T; g.A_q = A_q; g.A_t0 = A_t0; g.C_q = C_q; g.C_t0 = C_t0; g.act = act;
         return g;
     }
+    void launch(const GemmArgs &g, cudaStream_t s) {
+        if (gemm_pair_) tc::launch_tc_gemm2(g, n_sm_, s);
+        else tc::launch_tc_gemm(g, n_sm_, s);
+    }
     void gemm(const Layer &L, const __half *A, __half *C, int Q, int T, int A_q, int A_t0, int C_q, int C_t0, int act, cudaStream_t s) {
-        tc::launch_tc_gemm(base_args(L, A, C, Q, T, A_q, A_t0, C_q, C_t0, act), n_sm_, s);
+        launch(base_args(L, A, C, Q, T, A_q, A_t0, C_q, C_t0, act), s);
     }
 };
 

@@ -25,6 +25,7 @@ __host__ __device__ constexpr size_t tiled_off(int row, int col, int R) {
 struct GemmArgs {
     const __half *A;
     const __half *B;
+    const __half *B2;   // CTA-pair image: per N-tile [rows 0..NT/2 | rows NT/2..NT], each half tiled with R = NT/2
     const float *bias;  // [Nc]
     __half *C;
     float *gains;
@@ -35,10 +36,13 @@ struct GemmArgs {
     int mt_count, T, A_q, A_t0, C_q, C_t0;
     int act;       // 0 none, 1 relu, 2 sigmoid
     int out_mode;
+    unsigned long long *trace;  // debug (FVAD_GEMM_TRACE): CTA 0 logs clock64 for its first 4 M-tiles, nullptr otherwise
     int dbg;       // experiments only (FVAD_GEMM_DBG): bit 0 epilogue does no work, bit 1 producer copies nothing
     int seq0, n_seq, Kchunks;  // scatter: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
 };
 void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s);
+// CTA-pair version (nn_tc_gemm2.cu), reads a.B2
+void launch_tc_gemm2(const GemmArgs &a, int n_sm, cudaStream_t s);
 
 // One GRU layer over 54 steps for Q tiles of 128 sequences.
 //   xp:   tiles [q][54] of 1200 columns: W x_t + Wb (+Rb for z,r), columns in chunk-interleaved order
@@ -65,6 +69,7 @@ struct PackArgs {
     int Q, seq0, n_seq, Kchunks;
 };
 void launch_tc_pack(const PackArgs &a, cudaStream_t s);
+void launch_tc_ctx_pack(const float *ctx, __half *A0, int SC, int K, cudaStream_t s);
 
 }  // namespace tc
 }  // namespace fvad

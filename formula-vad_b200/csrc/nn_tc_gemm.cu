@@ -30,6 +30,11 @@ constexpr int kGemmThreads = 256;
 // (measured: W1, which overlaps the scan, 12.3 ms vs W2 7.6 ms for the same GEMM).
 constexpr int kSmemTotal = 214 * 1024;
 
+// timeline probe (CTA 0, first 4 M-tiles): [kind][mtile][ntile][slab], kinds: 0 producer B issued, 1 MMA full ok,
+// 2 MMA issued, 3 epilogue acc_full ok (slab 0) / done (slab 1), 4 MMA acc_empty ok (slab 0)
+#define GEMM_TRACE(kind, im, j, sl) do { if (a.trace && blockIdx.x == 0 && (im) < 4) \
+    a.trace[(((kind) * 4 + (im)) * 8 + (j)) * 32 + (sl)] = (unsigned long long)clock64(); } while (0)
+
 struct GemmShared {
     uint64_t full[kMaxStages], empty[kMaxStages], a_full[kMaxSlabs], a_empty[kMaxSlabs], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
@@ -98,6 +103,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                             mbar_expect_tx(&sh->full[st], bb);
                             bulk_g2s(sB + (size_t)st * pl.stage_bytes, Bt + (size_t)(k0 / 8) * (NT * 16), bb, &sh->full[st]);
                         }
+                        GEMM_TRACE(0, im, j, sl);
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                 }
@@ -116,6 +122,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                     const uint32_t buf = work & 1;
                     mbar_wait(&sh->acc_empty[buf], ((work >> 1) & 1) ^ 1);
                     tc_fence_after();
+                    GEMM_TRACE(4, im, j, 0);
                     const uint32_t idesc = make_idesc_f16(kTileM, NT);
                     const uint32_t d = tmem + buf * 256;
                     const bool last_n = (j == a.n_tiles - 1);
@@ -124,6 +131,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                         if (j == 0) mbar_wait(&sh->a_full[sl], im & 1);
                         mbar_wait(&sh->full[st], ph);
                         tc_fence_after();
+                        GEMM_TRACE(1, im, j, sl);
                         const int k0 = sl * KS, nk = min(KS, a.K - k0) / 16;
                         const uint64_t bd0 = make_smem_desc(smem_u32(sB + (size_t)st * pl.stage_bytes), NT * 16, 128);
                         const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
@@ -135,6 +143,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                             if (kk < nk) mma_ss_lohi<true>(d, alo + kk * (2 * kTileM * 16 / 16), ahi, blo + kk * bstep, bhi, idesc);
                         mma_commit(&sh->empty[st]);               // B stage free once these MMAs have read it
                         if (last_n) mma_commit(&sh->a_empty[sl]); // A slab free for the next M-tile
+                        GEMM_TRACE(2, im, j, sl);
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                     mma_commit(&sh->acc_full[buf]);
@@ -148,6 +157,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
         const size_t c_tile_bytes = tile_bytes(a.Nc);
         float *tr = reinterpret_cast<float *>(smem + pl.tr_off) + wq * (32 * 33);  // OUT == 1: this warp's 32x32 transpose pad
         uint32_t work = 0;
+        int im = 0;
 
         // bias + activation of 8 consecutive columns starting at column `col` (absolute, multiple of 8)
         auto act8 = [&](const uint32_t *r, int col, float (&v)[8]) {
@@ -162,7 +172,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
             }
         };
 
-        for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x) {
+        for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
             const int q = mt / a.T, t = mt % a.T;
             uint8_t *Ct = nullptr;
             float *g0 = nullptr;   // OUT == 1: gains row of this warp's first sequence
@@ -182,6 +192,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                 const uint32_t buf = work & 1;
                 mbar_wait(&sh->acc_full[buf], (work >> 1) & 1);
                 tc_fence_after();
+                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 0);
                 const uint32_t tbase = tmem + buf * 256 + ((uint32_t)(wq * 32) << 16);
                 for (int c = 0; c < ((a.dbg & 1) ? 0 : NT); c += 32) {
                     uint32_t r[32];
@@ -230,6 +241,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                 }
                 tc_fence_before();
                 __syncwarp();
+                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 1);
                 if (lane == 0) mbar_arrive(&sh->acc_empty[buf]);
             }
         }
@@ -258,6 +270,7 @@ void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
     pl.a_bytes = a.K * 256;  // K/8 core columns x 2048 B
     const int tr_bytes = a.out_mode == 1 ? 4 * 32 * 33 * 4 : 0;
+    static_assert(sizeof(GemmShared) <= 1024, "barrier block");
     const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 1024;
     pl.KS = 64;
     for (;;) {

@@ -1,0 +1,324 @@
+// nn_tc_gemm2.cu -- the dense-layer GEMM of nn_tc_gemm.cu on CTA PAIRS (tcgen05 cta_group::2, M = 256).
+//
+// Why pairs: the one-CTA kernel keeps its 128-row A tile (102 KB at K = 400) resident and streams the weight
+// matrix through what is left of shared memory.  Its timeline (tools/gemm_trace.py, profiles/r01_gemm_timeline.txt)
+// shows the ring is bytes-in-flight bound: a 30 KB stage lands 1 400-2 400 cycles after it is requested, three
+// stages fit, the tensor pipe wants one every 480 cycles and gets one every ~830.  In a pair each CTA stores only
+// HALF of every weight stage (N/2 rows) -- the tensor cores of both SMs read both halves -- so the same ring holds
+// twice the look-ahead, the L2 stream per SM halves and so does the shared-memory write+read traffic.
+//
+// Same math, roles and epilogue as nn_tc_gemm.cu.  Differences: cluster (2,1,1); CTA rank r owns M-tile 2*pair + r;
+// only rank 0 issues MMAs and commits (multicast to both CTAs' barriers); a relay thread in the peer forwards its
+// `full` / `a_full` completions to the leader; the peer's epilogue releases accumulators on the leader's barrier.
+#include "nn_tc.cuh"
+#include "tc_dev.cuh"
+
+namespace fvad {
+namespace tc {
+
+namespace {
+
+constexpr int kMaxSlabs = 40;
+constexpr int kMaxStages = 8;
+constexpr int kGemmThreads = 256;
+constexpr int kSmemTotal = 214 * 1024;  // see nn_tc_gemm.cu: leaves room for the concurrently running VAD scan
+#define GEMM_TRACE(kind, im, j, sl) do { } while (0)
+
+struct GemmShared {
+    uint64_t full[kMaxStages], peer_full[kMaxStages], empty[kMaxStages];
+    uint64_t a_full[kMaxSlabs], peer_a_full[kMaxSlabs], a_empty[kMaxSlabs], acc_full[2], acc_empty[2];
+    uint32_t tmem_base;
+};
+
+struct GemmPlan {  // host-computed shared-memory plan (stage_bytes is per CTA: half of a weight stage)
+    int KS, n_slabs, n_stages, stage_bytes, a_bytes, bias_off, tr_off, sh_off, smem_bytes;
+};
+
+template <int ACT, int OUT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) tc_gemm2_kernel(const GemmArgs a, const GemmPlan pl) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t *sA = smem, *sB = smem + pl.a_bytes;
+    float *bias_s = reinterpret_cast<float *>(smem + pl.bias_off);
+    GemmShared *sh = reinterpret_cast<GemmShared *>(smem + pl.sh_off);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+    const int n_mpairs = (a.mt_count + 1) >> 1;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < pl.n_stages; ++i) {
+            mbar_init(&sh->full[i], 1);
+            mbar_init(&sh->peer_full[i], 1);
+            mbar_init(&sh->empty[i], 1);
+        }
+        for (int i = 0; i < pl.n_slabs; ++i) {
+            mbar_init(&sh->a_full[i], 1);
+            mbar_init(&sh->peer_a_full[i], 1);
+            mbar_init(&sh->a_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&sh->acc_full[i], 1);
+            mbar_init(&sh->acc_empty[i], 8);  // 4 epilogue warps in each CTA
+        }
+        fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < a.Nc; i += kGemmThreads) bias_s[i] = a.bias[i];
+    if (warp == 2) tmem_alloc2<512>(&sh->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();  // both CTAs' barriers and TMEM exist before any remote arrive / paired MMA
+    tc_fence_after();
+    const uint32_t tmem = sh->tmem_base;
+    const int KS = pl.KS, n_slabs = pl.n_slabs, n_stages = pl.n_stages;
+    const size_t a_tile_bytes = tile_bytes(a.K);
+
+    if (warp == 0) {
+        // ===== producer: this CTA's A tile and its half of every weight stage =====
+        if (elect_one()) {
+            uint32_t it = 0, st = 0, ph = 0, im = 0;
+            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+                const int mt = 2 * mp + (int)rank;
+                const bool valid = mt < a.mt_count;  // an odd tile count leaves the last pair's second tile as padding
+                const int q = mt / a.T, t = mt % a.T;
+                const uint8_t *At = reinterpret_cast<const uint8_t *>(a.A) + (size_t)(q * a.A_q + t + a.A_t0) * a_tile_bytes;
+                for (int j = 0; j < a.n_tiles; ++j) {
+                    const int NH = a.nt_size[j] >> 1;  // rows of this CTA's half
+                    const uint8_t *Bt = reinterpret_cast<const uint8_t *>(a.B2) + a.nt_off[j] + (size_t)rank * NH * a.K * 2;
+                    for (int sl = 0; sl < n_slabs; ++sl, ++it) {
+                        const int k0 = sl * KS, kw = min(KS, a.K - k0);
+                        if (j == 0) {
+                            mbar_wait_cluster(&sh->a_empty[sl], (im & 1) ^ 1);
+                            if (valid) {
+                                const uint32_t ab = (uint32_t)(kw / 8) * (kTileM * 16);
+                                mbar_expect_tx(&sh->a_full[sl], ab);
+                                bulk_g2s(sA + (size_t)(k0 / 8) * (kTileM * 16), At + (size_t)(k0 / 8) * (kTileM * 16), ab, &sh->a_full[sl]);
+                            } else {
+                                mbar_arrive(&sh->a_full[sl]);
+                            }
+                        }
+                        mbar_wait_cluster(&sh->empty[st], ph ^ 1);
+                        const uint32_t bb = (uint32_t)(kw / 8) * (NH * 16);
+                        mbar_expect_tx(&sh->full[st], bb);
+                        bulk_g2s(sB + (size_t)st * pl.stage_bytes, Bt + (size_t)(k0 / 8) * (NH * 16), bb, &sh->full[st]);
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
+                    }
+                }
+            }
+            // drain: the leader's multicast commits to this CTA's barriers must have landed before the CTA exits
+            for (uint32_t s = 0; s < (uint32_t)n_stages && s < it; ++s) {
+                const uint32_t last = ((it - 1 - s) / n_stages) * n_stages + s;
+                mbar_wait_cluster(&sh->empty[s], (last / n_stages) & 1);
+            }
+            if (im) for (int sl = 0; sl < n_slabs; ++sl) mbar_wait_cluster(&sh->a_empty[sl], (im - 1) & 1);
+        }
+    } else if (warp == 3) {
+        // ===== relay (peer only): forward this CTA's operand arrivals to the leader, in the issuer's order =====
+        if (!leader && elect_one()) {
+            uint32_t st = 0, ph = 0, im = 0;
+            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im)
+                for (int j = 0; j < a.n_tiles; ++j)
+                    for (int sl = 0; sl < n_slabs; ++sl) {
+                        if (j == 0) {
+                            mbar_wait(&sh->a_full[sl], im & 1);
+                            mbar_arrive_cluster(&sh->peer_a_full[sl], 0);
+                        }
+                        mbar_wait(&sh->full[st], ph);
+                        mbar_arrive_cluster(&sh->peer_full[st], 0);
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
+                    }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader only): 256 x NT x 16 per instruction =====
+        if (leader && elect_one()) {
+            uint32_t st = 0, ph = 0, work = 0, im = 0;
+            const uint64_t ad0 = make_smem_desc(smem_u32(sA), kTileM * 16, 128);
+            const uint32_t alo0 = (uint32_t)ad0, ahi = (uint32_t)(ad0 >> 32);
+            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+                for (int j = 0; j < a.n_tiles; ++j, ++work) {
+                    const int NT = a.nt_size[j], NH = NT >> 1;
+                    const uint32_t buf = work & 1;
+                    mbar_wait_cluster(&sh->acc_empty[buf], ((work >> 1) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t idesc = make_idesc_f16(2 * kTileM, NT);
+                    const uint32_t d = tmem + buf * 256;
+                    const bool last_n = (j == a.n_tiles - 1);
+                    const uint32_t bstep = 2u * (uint32_t)NH;  // one K-step of a half stage = 2 core columns = 2*NH*16 bytes
+                    for (int sl = 0; sl < n_slabs; ++sl) {
+                        if (j == 0) {
+                            mbar_wait(&sh->a_full[sl], im & 1);
+                            mbar_wait_cluster(&sh->peer_a_full[sl], im & 1);
+                        }
+                        mbar_wait(&sh->full[st], ph);
+                        mbar_wait_cluster(&sh->peer_full[st], ph);
+                        tc_fence_after();
+                        const int k0 = sl * KS, nk = min(KS, a.K - k0) / 16;
+                        const uint64_t bd0 = make_smem_desc(smem_u32(sB + (size_t)st * pl.stage_bytes), NH * 16, 128);
+                        const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
+                        const uint32_t alo = alo0 + (uint32_t)(k0 / 8) * (kTileM * 16 / 16);
+                        if (sl == 0) mma2_ss_lohi<false>(d, alo, ahi, blo, bhi, idesc);
+                        else mma2_ss_lohi<true>(d, alo, ahi, blo, bhi, idesc);
+#pragma unroll
+                        for (int kk = 1; kk < 4; ++kk)
+                            if (kk < nk) mma2_ss_lohi<true>(d, alo + kk * (2 * kTileM * 16 / 16), ahi, blo + kk * bstep, bhi, idesc);
+                        mma2_commit_mc(&sh->empty[st], 3);
+                        if (last_n) mma2_commit_mc(&sh->a_empty[sl], 3);
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
+                    }
+                    mma2_commit_mc(&sh->acc_full[buf], 3);
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue =====
+        const int wq = warp & 3;
+        const int row = wq * 32 + lane;
+        const size_t c_tile_bytes = tile_bytes(a.Nc);
+        float *tr = reinterpret_cast<float *>(smem + pl.tr_off) + wq * (32 * 33);  // OUT == 1: this warp's 32x32 transpose pad
+        uint32_t work = 0;
+        int im = 0;
+
+        // bias + activation of 8 consecutive columns starting at column `col` (absolute, multiple of 8)
+        auto act8 = [&](const uint32_t *r, int col, float (&v)[8]) {
+            const float4 b0 = *reinterpret_cast<const float4 *>(bias_s + col), b1 = *reinterpret_cast<const float4 *>(bias_s + col + 4);
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float x = __uint_as_float(r[i]) + b[i];
+                if (ACT == 1) x = fmaxf(x, 0.0f);
+                if (ACT == 2) x = __fdividef(1.0f, 1.0f + __expf(-x));
+                v[i] = x;
+            }
+        };
+
+        for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+            const int mt = 2 * mp + (int)rank;
+            const bool valid = mt < a.mt_count;
+            const int q = mt / a.T, t = mt % a.T;
+            uint8_t *Ct = nullptr;
+            float *g0 = nullptr;   // OUT == 1: gains row of this warp's first sequence
+            int rows_valid = 0;
+            if (OUT == 0) {
+                Ct = reinterpret_cast<uint8_t *>(a.C) + (size_t)(q * a.C_q + t + a.C_t0) * c_tile_bytes +
+                     (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16;
+            } else {
+                // gains are [sc][50*Kchunks][161] and sequence g = sc*Kchunks + jc owns frames 50*jc.. of stream-channel
+                // sc, so its frame t is row 50*g + t of the flat [.][161] array: consecutive sequences are 50 rows apart
+                const int gq = a.seq0 + q * kTileM + wq * 32;
+                rows_valid = min(32, a.n_seq - gq);
+                g0 = a.gains + ((size_t)kFrames * gq + (t + a.C_t0)) * kBins;
+            }
+            for (int j = 0; j < a.n_tiles; ++j, ++work) {
+                const int NT = a.nt_size[j], col0 = a.nt_col[j];
+                const uint32_t buf = work & 1;
+                mbar_wait_cluster(&sh->acc_full[buf], (work >> 1) & 1);
+                tc_fence_after();
+                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 0);
+                const uint32_t tbase = tmem + buf * 256 + ((uint32_t)(wq * 32) << 16);
+                for (int c = 0; c < (valid ? NT : 0); c += 32) {
+                    uint32_t r[32];
+                    const bool full32 = c + 32 <= NT;  // N-tiles are multiples of 16
+                    if (full32) {
+                        tmem_ld32(tbase + c, r);
+                    } else {
+                        uint32_t r16[16];
+                        tmem_ld16(tbase + c, r16);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { r[i] = r16[i]; r[16 + i] = 0; }
+                    }
+                    tmem_wait_ld();
+                    const int ng = full32 ? 4 : 2;  // groups of 8 columns
+                    if (OUT == 0) {
+#pragma unroll
+                        for (int gI = 0; gI < 4; ++gI) {
+                            if (gI < ng) {
+                                float v[8];
+                                act8(r + 8 * gI, col0 + c + 8 * gI, v);
+                                uint4 o;
+                                o.x = pack_h2(v[0], v[1]); o.y = pack_h2(v[2], v[3]); o.z = pack_h2(v[4], v[5]); o.w = pack_h2(v[6], v[7]);
+                                *reinterpret_cast<uint4 *>(Ct + (size_t)(((col0 + c) >> 3) + gI) * (kTileM * 16)) = o;
+                            }
+                        }
+                    } else {
+                        // thread = row: park the 32 columns in shared memory, then every lane writes one column of each
+                        // row so a row's 32 floats leave as one 128-byte store
+#pragma unroll
+                        for (int gI = 0; gI < 4; ++gI) {
+                            if (gI < ng) {
+                                float v[8];
+                                act8(r + 8 * gI, col0 + c + 8 * gI, v);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) tr[lane * 33 + 8 * gI + i] = v[i];
+                            }
+                        }
+                        __syncwarp();
+                        const int col = col0 + c + lane;
+                        if (col < a.n_valid && lane < 8 * ng) {
+                            float *gp = g0 + col;
+                            for (int rr = 0; rr < rows_valid; ++rr) gp[(size_t)rr * (kFrames * kBins)] = tr[rr * 33 + lane];
+                        }
+                        __syncwarp();
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 1);
+                if (lane == 0) mbar_arrive_cluster(&sh->acc_empty[buf], 0);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();  // neither CTA frees TMEM or exits while the other may still signal it
+    if (warp == 2) tmem_dealloc2<512>(tmem);
+}
+
+}  // namespace
+
+template <int ACT, int OUT>
+static void launch_variant2(const GemmArgs &a, const GemmPlan &pl, int grid, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) {
+        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm2_kernel<ACT, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        attr = true;
+    }
+    tc_gemm2_kernel<ACT, OUT><<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
+}
+
+void launch_tc_gemm2(const GemmArgs &a, int n_sm, cudaStream_t s) {
+    if (a.mt_count <= 0) return;
+    GemmPlan pl;
+    int nt_max = 0;
+    for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
+    pl.a_bytes = a.K * 256;  // K/8 core columns x 2048 B
+    const int tr_bytes = a.out_mode == 1 ? 4 * 32 * 33 * 4 : 0;
+    static_assert(sizeof(GemmShared) <= 2048, "barrier block");
+    const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 2048;
+    pl.KS = 64;
+    for (;;) {
+        pl.stage_bytes = (nt_max / 2) * pl.KS * 2;  // this CTA's half of a weight stage
+        pl.n_stages = (kSmemTotal - pl.a_bytes - fixed) / pl.stage_bytes;
+        if (pl.n_stages >= 3 || pl.KS == 16) break;  // fewer, larger stages: the per-stage barrier round trip costs the issuing thread more than the shorter ring
+        pl.KS /= 2;
+    }
+    if (pl.n_stages > kMaxStages) pl.n_stages = kMaxStages;
+    pl.n_slabs = (a.K + pl.KS - 1) / pl.KS;
+    if (pl.n_stages < 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: layer does not fit the shared-memory plan");
+    pl.bias_off = pl.a_bytes + pl.n_stages * pl.stage_bytes;
+    pl.tr_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
+    pl.sh_off = pl.tr_off + tr_bytes;
+    pl.smem_bytes = pl.sh_off + 2048;
+    const int n_mpairs = (a.mt_count + 1) / 2;
+    const int grid = 2 * (n_mpairs < n_sm / 2 ? n_mpairs : n_sm / 2);
+    if (a.out_mode == 1) {
+        if (a.act != 2) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: the gains output applies the sigmoid");
+        launch_variant2<2, 1>(a, pl, grid, s);
+    } else if (a.act == 0) launch_variant2<0, 0>(a, pl, grid, s);
+    else if (a.act == 1) launch_variant2<1, 0>(a, pl, grid, s);
+    else throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: unsupported activation/output combination");
+    FVAD_LAUNCHED();
+    FVAD_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace tc
+}  // namespace fvad

@@ -43,7 +43,9 @@ struct StftLaneConst {
 
 // frames f = warp, warp+10, ... of the tile xs -> spectrum rows / feature rows
 __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneConst &lc, const float *__restrict__ xs,
-                                            float2 *__restrict__ Z, int sc, int c, int warp, int lane) {
+                                            float2 *__restrict__ Z, __half *__restrict__ fh, int sc, int c, int warp, int lane) {
+    // fh: this warp's 176-half staging row for the fused NN input pack (bins 161..175 stay zero)
+    if (a.nn_tiles && lane < 15) fh[kBins + lane] = __float2half(0.0f);
     for (int f = warp; f < kFrames; f += kStftWarps) {
         const float *fx = xs + f * kHop;
         float2 v[5];
@@ -60,6 +62,19 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
         const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
         float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
         float *frw = a.feat + frow * kBins;
+        // fused NN input pack: element (sequence g, step t, bin k) of the fp16 tiles, see nn_tc.cuh tiled_off
+        constexpr size_t kTileBytes = 128 * 176 * 2;
+        __half *t0 = nullptr, *t1 = nullptr;
+        if (a.nn_tiles) {
+            const int g = sc * a.K + c;
+            t0 = reinterpret_cast<__half *>(static_cast<uint8_t *>(a.nn_tiles) + ((size_t)(g >> 7) * kSteps + (f + kCtx)) * kTileBytes +
+                                            (size_t)((g & 127) >> 3) * 128 + (size_t)(g & 7) * 16);
+            if (f >= kFrames - kCtx && c + 1 < a.K) {
+                const int g1 = g + 1;
+                t1 = reinterpret_cast<__half *>(static_cast<uint8_t *>(a.nn_tiles) + ((size_t)(g1 >> 7) * kSteps + (f - (kFrames - kCtx))) * kTileBytes +
+                                                (size_t)((g1 & 127) >> 3) * 128 + (size_t)(g1 & 7) * 16);
+            }
+        }
         // real-FFT unpack in kissfft's pair form (kiss_fftr.c:93-116): the lane handles bins k and 160-k for
         // k = lane + 32q in [0, 80].  k = 0 runs through the same arithmetic with Z[0] as its own partner
         // (gives DC = x + y, Nyquist = x - y, imaginary parts 0, kiss_fftr.c:82-89); at k = 80 both stores hit
@@ -77,9 +92,17 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
                     // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no
                     // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate)
                     const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
-                    frw[kk] = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
+                    const float ft = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
+                    frw[kk] = ft;
+                    if (t0) fh[kk] = __float2half_rn(ft);
                 }
             }
+        }
+        __syncwarp();
+        if (t0 && lane < 22) {  // 22 core columns of 8 bins: one 16-byte store each, 2 048 bytes apart
+            const uint4 v = *reinterpret_cast<const uint4 *>(fh + 8 * lane);
+            *reinterpret_cast<uint4 *>(reinterpret_cast<uint8_t *>(t0) + (size_t)lane * 2048) = v;
+            if (t1) *reinterpret_cast<uint4 *>(reinterpret_cast<uint8_t *>(t1) + (size_t)lane * 2048) = v;
         }
         __syncwarp();
     }
@@ -107,6 +130,7 @@ struct StftSmem1 {
     float win[kNfft];
     float2 zb[kStftWarps][kHop];
     float red[kStftWarps];
+    __align__(16) __half fh[kStftWarps][176];
     uint64_t full[2];
 };
 
@@ -161,20 +185,32 @@ __global__ void __launch_bounds__(kStftThreads, 2) stft_kernel_d1(StftArgs a, co
         }
         stft_sumsq(a, ss, sm.red, sc, c, tid);  // contains a __syncthreads: the halo rows are visible after it
         if (c == a.K - 1 && tid < kHop) a.halo_out[(size_t)sc * kHop + tid] = xs[kFrames * kHop + tid];
-        stft_frames(a, lc, xs, sm.zb[warp], sc, c, warp, lane);
+        stft_frames(a, lc, xs, sm.zb[warp], sm.fh[warp], sc, c, warp, lane);
         __syncthreads();
     }
 }
 
 // ---- general D (48 kHz input: D = 3): one chunk per CTA, decimating loads ----
+struct StftSmemD {
+    float xs[kXs];
+    float2 T[256];
+    float win[kNfft];
+    float2 zb[kStftWarps][kHop];
+    float red[kStftWarps];
+    __align__(16) __half fh[kStftWarps][176];
+};
+
 template <int D>
 __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const float2 *__restrict__ gT,
                                                             const float *__restrict__ gwin) {
-    __shared__ __align__(16) float xs[kXs];
-    __shared__ float2 T[256];  // indices used by the N=160 transform stay below 249
-    __shared__ float win[kNfft];
-    __shared__ float2 zb[kStftWarps][kHop];
-    __shared__ float red[kStftWarps];
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    StftSmemD &sm = *reinterpret_cast<StftSmemD *>(smem_raw);
+    float *xs = sm.xs;
+    float2 *T = sm.T;  // indices used by the N=160 transform stay below 249
+    float *win = sm.win;
+    auto &zb = sm.zb;
+    float *red = sm.red;
+    auto &fh = sm.fh;
 
     const int c = blockIdx.x;    // chunk within the span
     const int sc = blockIdx.y;   // stream-channel
@@ -224,7 +260,7 @@ __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const fl
 
     StftLaneConst lc;
     lc.init(T, win, lane);
-    stft_frames(a, lc, xs, zb[warp], sc, c, warp, lane);
+    stft_frames(a, lc, xs, zb[warp], fh[warp], sc, c, warp, lane);
 }
 
 void launch_stft(const StftArgs &a, const Tables &t, cudaStream_t s) {
@@ -238,8 +274,13 @@ void launch_stft(const StftArgs &a, const Tables &t, cudaStream_t s) {
         dim3 grid((unsigned)((a.K + kChunksPerCta - 1) / kChunksPerCta), (unsigned)a.SC);
         stft_kernel_d1<<<grid, kStftThreads, sizeof(StftSmem1), s>>>(a, t.T320, t.win320);
     } else if (a.D == 3) {
+        static bool attr3 = false;
+        if (!attr3) {
+            FVAD_CUDA_CHECK(cudaFuncSetAttribute(stft_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StftSmemD)));
+            attr3 = true;
+        }
         dim3 grid((unsigned)a.K, (unsigned)a.SC);
-        stft_kernel<3><<<grid, kStftThreads, 0, s>>>(a, t.T320, t.win320);
+        stft_kernel<3><<<grid, kStftThreads, sizeof(StftSmemD), s>>>(a, t.T320, t.win320);
     } else {
         throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "unsupported decimation factor");
     }
