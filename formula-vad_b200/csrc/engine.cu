@@ -134,6 +134,12 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
     for (auto &e : ev_) FVAD_CUDA_CHECK(cudaEventCreate(&e));
     FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&scan_done_, cudaEventDisableTiming));
     FVAD_CUDA_CHECK(cudaEventRecord(scan_done_, scan_stream_));
+    for (auto &e : scan_done_b_) {
+        FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        FVAD_CUDA_CHECK(cudaEventRecord(e, scan_stream_));
+    }
+    FVAD_CUDA_CHECK(cudaEventCreateWithFlags(&after_rnn_, cudaEventDisableTiming));
+    defer_scan_ = scan_stream_ != stream_ && !opt_.keep_taps && !getenv("FVAD_SCAN_EAGER");
     tables_.build();
     launches0_ = g_kernel_launches;
 
@@ -176,6 +182,8 @@ Batch::~Batch() {
     if (stream_) cudaStreamSynchronize(stream_);
     if (scan_stream_ && scan_stream_ != stream_) { cudaStreamSynchronize(scan_stream_); cudaStreamDestroy(scan_stream_); }
     if (scan_done_) cudaEventDestroy(scan_done_);
+    for (auto &e : scan_done_b_) if (e) cudaEventDestroy(e);
+    if (after_rnn_) cudaEventDestroy(after_rnn_);
     if (copy_stream_) { cudaStreamSynchronize(copy_stream_); cudaStreamDestroy(copy_stream_); }
     for (int i = 0; i < 2; ++i) {
         if (stage_ready_[i]) cudaEventDestroy(stage_ready_[i]);
@@ -234,9 +242,15 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
             const size_t f0 = (size_t)(processed_ / (uint64_t)chunk_) * kFrames;
             if (f0 + rows > opt_.forced_gain_frames) throw Error(FVAD_ERR_INVALID_ARGUMENT, "forced_gains shorter than the audio");
             launch_copy_rows(gains_.p, forced_.p + f0 * kBins, rows * kBins, opt_.forced_gain_frames * kBins, rows * kBins, (size_t)SC_, s);
+            if (pscan_.valid) issue_scan(nullptr);
         } else {
             NnSpan ns{feat_.p, gains_.p, SC_, K, ctx_carry_.p, sa.nn_tiles != nullptr};
+            // The previous span's VAD scan starts once this span's recurrent layers are queued: their epilogue
+            // warps are issue-bound, and a scan warp sharing an SM sub-partition with them stretched the whole
+            // GRU launch by a third, while the GEMMs and the spectral kernels that follow do not notice it.
+            if (pscan_.valid) ns.after_rnn = after_rnn_;
             nn_->forward(ns, s);
+            if (pscan_.valid) issue_scan(after_rnn_);
         }
         FVAD_CUDA_CHECK(cudaEventRecord(ev_[2], s));
 
@@ -250,42 +264,41 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
         launch_copy_rows(sumsq_.p, sumsq_carry_.p, (size_t)K + 1, 1, 1, (size_t)SC_, s);
         FVAD_CUDA_CHECK(cudaEventRecord(ev_[3], s));
 
-        // ---- K3b ----  (band_/ratio_/met_ are read by the previous span's scan on scan_stream_)
-        FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));
+        // ---- K3b ----  (band_/ratio_/met_[vb] were last read by the scan two spans back)
+        const int vb = vbuf_;
+        FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_b_[vb], 0));
         const uint64_t frames_end = span_end / (uint64_t)fft_size_;
         n_frames = (int)(frames_end - frames_done_);
         if (n_frames > 0) {
             if (n_frames > max_frames_) {
-                FVAD_CUDA_CHECK(cudaStreamSynchronize(scan_stream_));  // the previous scan still reads the old buffers
+                if (pscan_.valid) issue_scan(nullptr);
+                FVAD_CUDA_CHECK(cudaStreamSynchronize(scan_stream_));  // earlier scans still read the old buffers
                 max_frames_ = n_frames + 64;
-                band_.ensure((size_t)n_bands_ * S_ * max_frames_);
-                ratio_.ensure((size_t)S_ * max_frames_);
-                met_.ensure((size_t)S_ * max_frames_);
+                for (int b = 0; b < 2; ++b) {
+                    band_[b].ensure((size_t)n_bands_ * S_ * max_frames_);
+                    ratio_[b].ensure((size_t)S_ * max_frames_);
+                    met_[b].ensure((size_t)S_ * max_frames_);
+                }
             }
             VadFftArgs va;
-            va.y16 = y16_.p; va.sumsq = sumsq_.p; va.band = band_.p; va.ratio = ratio_.p;
+            va.y16 = y16_.p; va.sumsq = sumsq_.p; va.band = band_[vb].p; va.ratio = ratio_[vb].p;
             va.band_lo = band_lo_.p; va.band_hi = band_hi_.p; va.n_bands = n_bands_;
             va.S = S_; va.C = C_; va.K = K; va.D = D_;
             va.span_start = (long long)span_start; va.first_frame = (long long)frames_done_;
             va.n_frames = n_frames; va.max_frames = max_frames_; va.fft_size = fft_size_; va.chunk = chunk_;
             va.has_prev_chunk = span_start > 0;
+            work_ctr_.ensure(4);
+            va.work_ctr = work_ctr_.p;
             launch_vadfft(va, tables_, s);
         }
         FVAD_CUDA_CHECK(cudaEventRecord(ev_[4], s));
 
-        // ---- K4 ----  on its own stream: a latency-bound scan that overlaps the next span's network
-        FVAD_CUDA_CHECK(cudaStreamWaitEvent(scan_stream_, ev_[4], 0));
-        FVAD_CUDA_CHECK(cudaEventRecord(ev_[5], scan_stream_));
-        if (n_frames > 0) {
-            ScanArgs ca;
-            ca.band = band_.p; ca.ratio = ratio_.p; ca.machines = d_machines_.p; ca.states = d_states_.p;
-            ca.rings = rings_.p; ca.ring_pitch = ring_pitch_; ca.segments = d_segments_.p; ca.max_segments = max_segments_;
-            ca.met = met_.p; ca.S = S_; ca.M = M_; ca.n_frames = n_frames; ca.max_frames = max_frames_;
-            ca.first_frame = (long long)frames_done_; ca.fft_size = fft_size_; ca.fast = scan_fast_;
-            launch_vadscan(ca, scan_stream_);
-        }
-        FVAD_CUDA_CHECK(cudaEventRecord(ev_[6], scan_stream_));
-        FVAD_CUDA_CHECK(cudaEventRecord(scan_done_, scan_stream_));
+        // ---- K4 ----  on its own stream: a latency-bound scan that overlaps the next span's kernels
+        if (pscan_.valid) issue_scan(nullptr);  // (only when the span above had no network launch)
+        pscan_.valid = true; pscan_.buf = vb; pscan_.n_frames = n_frames;
+        pscan_.first_frame = (long long)frames_done_; pscan_.span = span_idx_ - 1;
+        if (n_frames > 0) vbuf_ ^= 1;
+        if (!defer_scan_ || n_frames <= 0) issue_scan(nullptr);
         if (opt_.keep_taps) FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));  // the taps below copy met_
     }
 
@@ -303,9 +316,9 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
             launch_upsample(y16_.p + kYLook, ypitch, taps_.den.p + (size_t)chunk_ * taps_.fill_chunks, (size_t)chunk_ * taps_.cap_chunks,
                             (size_t)kChunk16 * K, D_, SC_, s);
             if (n_frames > 0 && taps_.fill_vad + n_frames <= taps_.cap_vad) {
-                launch_copy_rows(taps_.band.p + taps_.fill_vad, band_.p, taps_.cap_vad, max_frames_, (size_t)n_frames, (size_t)S_, s);
-                launch_copy_rows(taps_.ratio.p + taps_.fill_vad, ratio_.p, taps_.cap_vad, max_frames_, (size_t)n_frames, (size_t)S_, s);
-                FVAD_CUDA_CHECK(cudaMemcpy2DAsync(taps_.met.p + taps_.fill_vad, taps_.cap_vad, met_.p, (size_t)max_frames_,
+                launch_copy_rows(taps_.band.p + taps_.fill_vad, band_[vbuf_ ^ 1].p, taps_.cap_vad, max_frames_, (size_t)n_frames, (size_t)S_, s);
+                launch_copy_rows(taps_.ratio.p + taps_.fill_vad, ratio_[vbuf_ ^ 1].p, taps_.cap_vad, max_frames_, (size_t)n_frames, (size_t)S_, s);
+                FVAD_CUDA_CHECK(cudaMemcpy2DAsync(taps_.met.p + taps_.fill_vad, taps_.cap_vad, met_[vbuf_ ^ 1].p, (size_t)max_frames_,
                                                   (size_t)n_frames, (size_t)S_, cudaMemcpyDeviceToDevice, s));
                 taps_.fill_vad += n_frames;
             }
@@ -325,6 +338,26 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
     chunks_processed_ += (uint64_t)K * SC_;
 }
 
+// Queue the held scan on scan_stream_: after its own span's K3b, and after `also_after` when given.
+void Batch::issue_scan(cudaEvent_t also_after) {
+    const PendingScan p = pscan_;
+    pscan_.valid = false;
+    cudaEvent_t *ev = span_ev_[p.span].data();
+    FVAD_CUDA_CHECK(cudaStreamWaitEvent(scan_stream_, ev[4], 0));
+    if (also_after) FVAD_CUDA_CHECK(cudaStreamWaitEvent(scan_stream_, also_after, 0));
+    FVAD_CUDA_CHECK(cudaEventRecord(ev[5], scan_stream_));
+    if (p.n_frames > 0) {
+        ScanArgs ca;
+        ca.band = band_[p.buf].p; ca.ratio = ratio_[p.buf].p; ca.machines = d_machines_.p; ca.states = d_states_.p;
+        ca.rings = rings_.p; ca.ring_pitch = ring_pitch_; ca.segments = d_segments_.p; ca.max_segments = max_segments_;
+        ca.met = met_[p.buf].p; ca.S = S_; ca.M = M_; ca.n_frames = p.n_frames; ca.max_frames = max_frames_;
+        ca.first_frame = p.first_frame; ca.fft_size = fft_size_; ca.fast = scan_fast_;
+        launch_vadscan(ca, scan_stream_);
+    }
+    FVAD_CUDA_CHECK(cudaEventRecord(ev[6], scan_stream_));
+    FVAD_CUDA_CHECK(cudaEventRecord(scan_done_, scan_stream_));
+    if (p.n_frames > 0) FVAD_CUDA_CHECK(cudaEventRecord(scan_done_b_[p.buf], scan_stream_));
+}
 
 // Ingest + run.  Host memory (and 16-bit PCM) goes through two stage buffers: the copy stream fills
 // buffer b with span i+1 while the compute stream runs span i out of buffer b^1, so H2D overlaps the
@@ -451,6 +484,7 @@ void Batch::push_any(const void *const *pcm, size_t n_pointers, size_t n, int me
     if (n_left && fmt) launch_i16_to_f32(pend_.p + pend_dst, pend_i16_.p, (size_t)chunk_, (size_t)chunk_, n_left, (size_t)SC_, s);
     n_pend_ = (int)left;
 
+    if (pscan_.valid) issue_scan(nullptr);
     FVAD_CUDA_CHECK(cudaStreamWaitEvent(s, scan_done_, 0));
     if (Ktot > 0 && !opt_.stft_only) fetch_segments();
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[7], s));

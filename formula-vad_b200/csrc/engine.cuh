@@ -61,7 +61,14 @@ private:
     fvad_batch_options opt_;
     int Kmax_;
     cudaStream_t stream_ = nullptr, scan_stream_ = nullptr, copy_stream_ = nullptr;
-    cudaEvent_t scan_done_ = nullptr;
+    cudaEvent_t scan_done_ = nullptr;          // the most recently queued scan
+    cudaEvent_t scan_done_b_[2] = {};          // the scan that last read band_/ratio_/met_[b]
+    cudaEvent_t after_rnn_ = nullptr;          // NnSpan::after_rnn of the span in flight
+    // The scan of span i is queued behind the recurrent layers of span i+1 (see process_span), so it is held here
+    struct PendingScan { bool valid = false; int buf = 0, n_frames = 0; long long first_frame = 0; size_t span = 0; } pscan_;
+    int vbuf_ = 0;                              // band_/ratio_/met_ buffer the next span's K3b writes
+    bool defer_scan_ = true;
+    void issue_scan(cudaEvent_t also_after);
     cudaEvent_t stage_ready_[2] = {}, stage_free_[2] = {};  // double-buffered ingest: copy stream <-> compute stream
     cudaEvent_t ev_[8] = {};
     std::vector<std::array<cudaEvent_t, 7>> span_ev_;  // per-span stage boundaries of the current push
@@ -87,8 +94,9 @@ private:
     DevBuf<float> halo_[2], tail_[2];          // [SC][160]
     DevBuf<float> ctx_carry_, ylook_carry_, sumsq_carry_;
     DevBuf<fvad_complex> spec_;
-    DevBuf<float> feat_, gains_, y16_, sumsq_, band_, ratio_;
-    DevBuf<unsigned char> met_;
+    DevBuf<float> feat_, gains_, y16_, sumsq_, band_[2], ratio_[2];
+    DevBuf<unsigned char> met_[2];
+    DevBuf<unsigned long long> work_ctr_;  // dynamic work queues of the persistent spectral kernels
     DevBuf<int> band_lo_, band_hi_;
     DevBuf<ScanMachine> d_machines_;
     DevBuf<ScanState> d_states_;

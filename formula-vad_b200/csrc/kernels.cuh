@@ -59,6 +59,7 @@ struct VadFftArgs {
     int fft_size;          // 1024
     int chunk;             // D*8000
     int has_prev_chunk;    // slot 0 of sumsq valid
+    unsigned long long *work_ctr = nullptr;  // device scratch for the dynamic item queue (nullptr: static striding)
 };
 void launch_vadfft(const VadFftArgs &a, const Tables &t, cudaStream_t s);
 

@@ -27,6 +27,8 @@ struct NnSpan {
     int SC, K;
     const float *ctx;   // [SC][4][161] context rows of each stream-channel's first chunk (only read when tiles_ready)
     bool tiles_ready;   // the STFT already wrote the backend's input tiles (input_tiles()) for rows it owns
+    cudaEvent_t after_rnn = nullptr;  // recorded on the stream once the span's last recurrent launch is queued (or at the
+                                      // end of forward): the engine starts the previous span's VAD scan there
 };
 
 class NnBackend {

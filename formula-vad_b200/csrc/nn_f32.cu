@@ -167,6 +167,7 @@ public:
             gemm(f2.p, F2, dense, fc3_w.p, fc3_b.p, f3.p, F3, dense, M50, F3, F2, 1, s);
             gemm(f3.p, F3, dense, fc4_w.p, fc4_b.p, sp.gains, B, scat, M50, B, F3, 2, s);
         }
+        if (sp.after_rnn) FVAD_CUDA_CHECK(cudaEventRecord(sp.after_rnn, s));
     }
 
 private:

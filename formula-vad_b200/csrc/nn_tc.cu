@@ -239,6 +239,7 @@ public:
             mark(5, s);
             gru(1, h2_.p, Q, kCtx, s);
             mark(6, s);
+            if (sp.after_rnn && q0 + QB >= q_total) FVAD_CUDA_CHECK(cudaEventRecord(sp.after_rnn, s));
             gemm(fc2_, h2_.p, f2_.p, Q, kFrames, kSteps, kCtx, kFrames, 0, 1, s);
             mark(7, s);
             gemm(fc3_, f2_.p, f3_.p, Q, kFrames, kFrames, 0, kFrames, 0, 1, s);

@@ -76,7 +76,22 @@ __global__ void __launch_bounds__(kVadThreads, D == 1 ? 2 : 1) vadfft_kernel(Vad
     const long long n_items = (long long)a.n_frames * a.S;
     float2 *Z = zb[warp];
 
-    for (long long item = (long long)blockIdx.x * kVadWarps + warp; item < n_items; item += (long long)gridDim.x * kVadWarps) {
+    // Work queue: every warp starts on its own item, then draws kGrab more at a time from a counter.  (The VAD scan
+    // of the previous span shares some SMs with this launch; with static striding those SMs' warps set the tail.)
+    constexpr int kGrab = 4;
+    const long long n_static = (long long)gridDim.x * kVadWarps;
+    long long item = (long long)blockIdx.x * kVadWarps + warp, grab_end = item + 1;
+    for (;; ++item) {
+        if (item >= grab_end) {
+            if (!a.work_ctr) { item += n_static - 1; grab_end = item + 1; }
+            else {
+                unsigned long long g = 0;
+                if (lane == 0) g = atomicAdd(a.work_ctr, (unsigned long long)kGrab);
+                item = n_static + (long long)__shfl_sync(0xffffffffu, g, 0);
+                grab_end = item + kGrab;
+            }
+        }
+        if (item >= n_items) break;
         const int fi = (int)(item % a.n_frames);  // frame within this launch (fastest: neighbouring warps read neighbouring audio)
         const int s = (int)(item / a.n_frames);
         const long long frame = a.first_frame + fi;
@@ -166,6 +181,7 @@ void launch_vadfft(const VadFftArgs &a, const Tables &t, cudaStream_t s) {
     if (a.fft_size != 1024) throw Error(FVAD_ERR_INVALID_FFT_SIZE, "GPU VAD path supports fft_size 1024");
     const long long items = (long long)a.n_frames * a.S;
     const unsigned grid = (unsigned)std::min<long long>((items + kVadWarps - 1) / kVadWarps, 148 * (a.D == 1 ? 2 : 1));
+    if (a.work_ctr) FVAD_CUDA_CHECK(cudaMemsetAsync(a.work_ctr, 0, sizeof(unsigned long long), s));
     if (a.D == 1) vadfft_kernel<1><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
     else if (a.D == 3) vadfft_kernel<3><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
     else throw Error(FVAD_ERR_INVALID_SAMPLE_RATE, "unsupported upsample factor");

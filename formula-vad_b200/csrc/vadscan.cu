@@ -152,6 +152,26 @@ __device__ __forceinline__ double window_mean(const float *newest, int n, int pm
     return acc;
 }
 
+// The long-term recurrence, run by RUNS instead of by frames.  Between two threshold crossings the recurrence
+// has a closed form: while no frame meets the threshold every frame is pushed, so the running sum before frame
+// l is sum + prefix(new - evicted) and all 32 thresholds of a block come from one warp prefix sum; while every
+// frame meets it nothing changes at all.  Each iteration assumes "no frame met" from the cursor on, finds the
+// first lane that contradicts it, commits the pushes before that lane, then assumes "every frame met" and finds
+// the first lane that contradicts that.  Speech and silence come in runs of hundreds of frames, so a block of
+// 32 frames usually takes one or two iterations (~10 cycles a frame against ~95 for the frame-by-frame chain);
+// after kMaxIters iterations in one block (a decision flickering frame by frame) lane 0 finishes the block
+// sequentially.  The prefix sum associates the f64 additions differently from the sequential running sum: both
+// are exact while the window's dynamic range stays below 2^29 / n_long and differ by ~1e-16 relative beyond.
+constexpr int kMaxIters = 6;
+
+struct LongRun {       // warp-uniform copy of the long-term ring's state
+    double sum, last_avg, inv;
+    int idx, cnt, has_last;
+    int k;             // pushes since the eviction candidates were staged
+};
+
+__device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
 __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) {
     __shared__ float s_rb[kBatch];
     __shared__ double s_lw[kBatch + 2], s_st[kBatch], s_vr[kBatch];
@@ -170,12 +190,14 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
     const int hs = mc.n_short - 1, hr = mc.n_ratio - 1;
     for (int k = lane; k < hs; k += 32) x_s[k] = (float)ring_short[k];
     for (int k = lane; k < hr; k += 32) x_r[k] = (float)ring_ratio[k];
-    double inv_long = 1.0 / (double)(st.long_cnt > 0 ? st.long_cnt : 1);
     unsigned long long index = (unsigned long long)a.first_frame * (unsigned long long)a.fft_size;
+    LongRun L;
+    L.sum = st.long_sum; L.last_avg = st.last_avg; L.idx = st.long_idx; L.cnt = st.long_cnt; L.has_last = st.has_last;
+    L.inv = 1.0 / (double)(L.cnt > 0 ? L.cnt : 1);
+    L.k = 0;
 
     for (int i0 = 0; i0 < a.n_frames; i0 += kBatch) {
         const int nb = min(kBatch, a.n_frames - i0);
-        const int lidx = __shfl_sync(0xffffffffu, st.long_idx, 0);
         for (int j = lane; j < nb; j += 32) {
             x_s[hs + j] = band[i0 + j];
             const float r = ratio[i0 + j];
@@ -183,47 +205,112 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
             s_rb[j] = r;
         }
         for (int j = lane; j < nb + 2; j += 32) {
-            int li = lidx + j;
+            int li = L.idx + j;
             if (li >= mc.n_long) li -= mc.n_long;
             s_lw[j] = ring_long[li];
         }
+        L.k = 0;
         __syncwarp();
         for (int j = lane; j < nb; j += 32) {
             s_st[j] = window_mean(x_s + hs + j, mc.n_short, (st.short_idx + j) % mc.n_short, min(st.short_cnt + j + 1, mc.n_short));
             s_vr[j] = window_mean(x_r + hr + j, mc.n_ratio, (st.ratio_idx + j) % mc.n_ratio, min(st.ratio_cnt + j + 1, mc.n_ratio));
         }
         __syncwarp();
-        if (lane == 0) {
-            int k = 0;
-            double cur = s_lw[0], nxt = s_lw[1];
-#pragma unroll 2
-            for (int j = 0; j < nb; ++j) {
-                const float min_volume = x_s[hs + j], meta_ratio = s_rb[j];
-                const double short_term = s_st[j], vol_ratio = s_vr[j];
-                // VADMachine.zig:165-178
-                const double base = st.has_last ? st.last_avg : (mc.has_init ? mc.init_avg : short_term);
-                const double threshold = base * mc.threshold_factor;
-                const bool met = (short_term > threshold) && (vol_ratio > mc.ratio_threshold);
-                if (!met) {
-                    const double nv = (double)min_volume;
-                    const double old = (st.long_cnt == mc.n_long) ? cur : 0.0;
-                    st.long_sum = (st.long_sum - old) + nv;
-                    ring_long[st.long_idx] = nv;
-                    st.long_idx = (st.long_idx + 1 == mc.n_long) ? 0 : st.long_idx + 1;
-                    if (st.long_cnt < mc.n_long) {
-                        ++st.long_cnt;
-                        inv_long = 1.0 / (double)st.long_cnt;
+
+        for (int jb = 0; jb < nb; jb += 32) {
+            const int nl = min(32, nb - jb);
+            const int j = jb + lane;
+            const bool valid = lane < nl;
+            const float nvf = valid ? x_s[hs + j] : 0.0f;
+            const double stv = valid ? s_st[j] : 0.0;
+            const bool vrok = valid && (s_vr[j] > mc.ratio_threshold);
+            unsigned metmask = 0;
+            int cur = 0;
+            if (L.has_last && L.cnt == mc.n_long) {
+                for (int it = 0; it < kMaxIters && cur < nl; ++it) {
+                    // ---- no frame from the cursor on meets the threshold: every one of them is pushed ----
+                    const int rel = lane - cur;
+                    const bool act = rel >= 0 && valid;
+                    const double d = act ? (double)nvf - s_lw[L.k + rel] : 0.0;
+                    double inc = d;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const double up = __shfl_up_sync(0xffffffffu, inc, o);
+                        if (lane >= o) inc += up;
                     }
-                    st.last_avg = st.long_sum * inv_long;
-                    st.has_last = 1;
-                    ++k;
-                    cur = nxt;
-                    nxt = s_lw[k + 1];
+                    double exc = __shfl_up_sync(0xffffffffu, inc, 1);
+                    if (lane == 0) exc = 0.0;
+                    const double base = (rel == 0) ? L.last_avg : (L.sum + exc) * L.inv;
+                    const bool mA = act && (stv > base * mc.threshold_factor) && vrok;
+                    const unsigned hit = __ballot_sync(0xffffffffu, mA);
+                    const int f = hit ? __ffs((int)hit) - 1 : nl;
+                    const int np = f - cur;
+                    if (np > 0) {
+                        if (act && lane < f) {
+                            int li = L.idx + rel;
+                            if (li >= mc.n_long) li -= mc.n_long;
+                            ring_long[li] = (double)nvf;
+                        }
+                        L.sum += shfl_d(inc, f - 1);
+                        L.last_avg = L.sum * L.inv;
+                        L.idx += np;
+                        if (L.idx >= mc.n_long) L.idx -= mc.n_long;
+                        L.k += np;
+                    }
+                    cur = f;
+                    if (cur >= nl) break;
+                    // ---- every frame from the cursor on meets it: the long-term mean is frozen ----
+                    const bool mB = (stv > L.last_avg * mc.threshold_factor) && vrok;
+                    const unsigned stop = __ballot_sync(0xffffffffu, !mB && lane >= cur && valid);
+                    const int g = stop ? __ffs((int)stop) - 1 : nl;
+                    metmask |= (g >= 32 ? 0xffffffffu : ((1u << g) - 1u)) & ~((1u << cur) - 1u);
+                    cur = g;
                 }
-                if (met_out) met_out[i0 + j] = met ? 1 : 0;
-                if (met || st.state != ST_CLOSED)  // closed and not met: nothing changes (VADMachine.zig:190-196)
-                    fsm_step(st, mc, met, meta_ratio, index, segs, a.max_segments);
-                index += (unsigned long long)a.fft_size;
+            }
+            if (cur < nl) {
+                // frame by frame on lane 0: before the ring is full / the first push, or a flickering block
+                if (lane == 0) {
+                    for (int l = cur; l < nl; ++l) {
+                        const float min_volume = x_s[hs + jb + l];
+                        const double short_term = s_st[jb + l];
+                        // VADMachine.zig:165-178
+                        const double base = L.has_last ? L.last_avg : (mc.has_init ? mc.init_avg : short_term);
+                        const bool met = (short_term > base * mc.threshold_factor) && (s_vr[jb + l] > mc.ratio_threshold);
+                        if (!met) {
+                            const double nv = (double)min_volume;
+                            const double old = (L.cnt == mc.n_long) ? s_lw[L.k] : 0.0;
+                            L.sum = (L.sum - old) + nv;
+                            ring_long[L.idx] = nv;
+                            L.idx = (L.idx + 1 == mc.n_long) ? 0 : L.idx + 1;
+                            if (L.cnt < mc.n_long) {
+                                ++L.cnt;
+                                L.inv = 1.0 / (double)L.cnt;
+                            }
+                            L.last_avg = L.sum * L.inv;
+                            L.has_last = 1;
+                            ++L.k;
+                        } else {
+                            metmask |= 1u << l;
+                        }
+                    }
+                }
+                L.sum = shfl_d(L.sum, 0); L.last_avg = shfl_d(L.last_avg, 0); L.inv = shfl_d(L.inv, 0);
+                L.idx = __shfl_sync(0xffffffffu, L.idx, 0); L.cnt = __shfl_sync(0xffffffffu, L.cnt, 0);
+                L.has_last = __shfl_sync(0xffffffffu, L.has_last, 0); L.k = __shfl_sync(0xffffffffu, L.k, 0);
+                metmask = __shfl_sync(0xffffffffu, metmask, 0);
+            }
+            if (met_out && valid) met_out[i0 + j] = (unsigned char)((metmask >> lane) & 1u);
+            // ---- state machine + statistics: sequential, but idle while closed with nothing met ----
+            if (lane == 0) {
+                if (metmask == 0 && st.state == ST_CLOSED) {  // VADMachine.zig:190-196: nothing changes
+                    index += (unsigned long long)nl * (unsigned long long)a.fft_size;
+                } else {
+                    for (int l = 0; l < nl; ++l) {
+                        const bool met = (metmask >> l) & 1u;
+                        if (met || st.state != ST_CLOSED) fsm_step(st, mc, met, s_rb[jb + l], index, segs, a.max_segments);
+                        index += (unsigned long long)a.fft_size;
+                    }
+                }
             }
         }
         // ring counters advance identically on every lane; histories shift by nb
@@ -246,7 +333,10 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
     }
     for (int k = lane; k < hs; k += 32) ring_short[k] = (double)x_s[k];
     for (int k = lane; k < hr; k += 32) ring_ratio[k] = (double)x_r[k];
-    if (lane == 0) a.states[t] = st;
+    if (lane == 0) {
+        st.long_sum = L.sum; st.last_avg = L.last_avg; st.long_idx = L.idx; st.long_cnt = L.cnt; st.has_last = L.has_last;
+        a.states[t] = st;
+    }
 }
 
 void launch_vadscan(const ScanArgs &a, cudaStream_t s) {
@@ -254,10 +344,9 @@ void launch_vadscan(const ScanArgs &a, cudaStream_t s) {
     const int total = a.S * a.M;
     static bool attr = false;
     if (!attr) {
-        // The scan runs on its own stream next to the persistent NSNet2 kernels of the following span, which need
-        // ~200 KB of shared memory per SM.  An SM whose L1/shared split was set up for this small kernel cannot take
-        // one of their CTAs until the scan's CTA leaves (measured: +35 % on the overlapped GRU launch), so ask for
-        // the maximum shared-memory carveout here and the two kinds of CTA share an SM.
+        // The scan runs on its own stream next to the persistent NSNet2 kernels of the following span (~200 KB of
+        // shared memory per SM): keep the shared-memory carveout at its maximum so both kinds of CTA fit one SM.
+        // (What the scan does disturb is the GRU's issue-bound epilogue; the engine schedules around that.)
         cudaFuncSetAttribute(vadscan_warp_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(vadscan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr = true;
