@@ -6,5 +6,5 @@ The compute lives in csrc/ (hand-written sm_100a CUDA behind the C ABI of includ
 this package is the thin host-side mirror of the reference's AudioPipeline / FFT / NSNet2 surface.
 """
 from . import capi, sharding, synth, weights  # noqa: F401
-from .pipeline import (FFT, NSNet2, AudioPipeline, BatchPipeline, Evaluator, FvadError, eval_config,  # noqa: F401
+from .pipeline import (FFT, NSNet2, AudioPipeline, BatchPipeline, Evaluator, VADMachine, FvadError, eval_config,  # noqa: F401
                        vad_machine_config)

@@ -81,7 +81,7 @@ EXPORTS = (
     "fvad_pipeline_destroy", "fvad_pipeline_push_samples", "fvad_pipeline_total_write_count",
     "fvad_pipeline_segments", "fvad_batch_options_default", "fvad_batch_create", "fvad_batch_destroy",
     "fvad_batch_push", "fvad_batch_push_i16", "fvad_batch_segments", "fvad_batch_tap", "fvad_batch_stats_get",
-    "fvad_eval_config_default", "fvad_evaluate", "fvad_batch_evaluate",
+    "fvad_eval_config_default", "fvad_evaluate", "fvad_batch_evaluate", "fvad_vad_machine_scan",
 )
 
 
@@ -174,6 +174,8 @@ def lib():
     sig("fvad_eval_config_default", None, C.POINTER(EvalConfig))
     sig("fvad_evaluate", i32, C.POINTER(EvalSegment), sz, C.POINTER(EvalSegment), sz, C.POINTER(EvalConfig), C.POINTER(EvalStats))
     sig("fvad_batch_evaluate", i32, vp, C.POINTER(EvalSegment), C.POINTER(sz), C.POINTER(EvalConfig), C.POINTER(EvalStats))
+    sig("fvad_vad_machine_scan", i32, C.POINTER(VadMachineConfig), sz, sz, sz, c_f32p, c_f32p, sz, sz, vp, C.POINTER(Segment), sz,
+        C.POINTER(sz))
     _lib = L
     return L
 

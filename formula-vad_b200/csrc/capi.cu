@@ -523,6 +523,16 @@ int fvad_evaluate(const fvad_eval_segment *vad, size_t n_vad, const fvad_eval_se
     });
 }
 
+int fvad_vad_machine_scan(const fvad_vad_machine_config *cfgs, size_t n_machines, size_t sample_rate, size_t fft_size,
+                          const float *band_min, const float *ratio, size_t n_frames, size_t frames_per_launch, uint8_t *met,
+                          fvad_segment *segments, size_t max_segments, size_t *n_segments) {
+    return guarded([&] {
+        if (fft_size == 0 || sample_rate == 0) throw Error(FVAD_ERR_INVALID_ARGUMENT, "sample_rate and fft_size must be positive");
+        vad_machine_scan(cfgs, n_machines, sample_rate, fft_size, band_min, ratio, n_frames, frames_per_launch, met, segments,
+                         max_segments, n_segments);
+    });
+}
+
 int fvad_batch_evaluate(fvad_batch *b, const fvad_eval_segment *refs, const size_t *ref_offsets, const fvad_eval_config *cfg,
                         fvad_eval_stats *out) {
     return guarded([&] {

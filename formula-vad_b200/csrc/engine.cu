@@ -46,6 +46,80 @@ __global__ void init_scan_kernel(ScanState *states, double *rings, const ScanMac
 
 }  // namespace
 
+// VADMachine.init, reference src/AudioPipeline/VADMachine.zig:75-106 (f32 products, truncation)
+ScanMachine derive_machine(const fvad_vad_machine_config &c, size_t sample_rate, size_t fft_size) {
+    ScanMachine d;
+    memset(&d, 0, sizeof(d));
+    const float sr_f = (float)sample_rate, fft_f = (float)fft_size;
+    const float evals = sr_f / fft_f;
+    d.n_long = std::max<long long>(1, (long long)(evals * c.long_term_speech_avg_sec));
+    d.n_short = std::max<long long>(1, (long long)(evals * c.short_term_speech_avg_sec));
+    d.n_ratio = std::max<long long>(1, (long long)(evals * c.channel_vol_ratio_avg_sec));  // reference: no max(1); 0 would trap
+    d.has_init = c.has_initial_long_term_avg;
+    d.init_avg = c.initial_long_term_avg;
+    d.threshold_factor = (double)c.speech_threshold_factor;
+    d.ratio_threshold = (double)c.channel_vol_ratio_threshold;
+    // VADMachine.run :160-163, getOffsetRecording{Start,End} :312-325
+    d.min_to_open = (unsigned long long)(sr_f * c.min_consecutive_sec_to_open);
+    d.max_gap = (unsigned long long)(sr_f * c.max_speech_gap_sec);
+    d.start_margin = d.end_margin = (unsigned long long)(sr_f * 2);
+    d.min_duration_sec = c.min_vad_duration_sec;
+    d.frame_sec = fft_f / sr_f;  // trackSpeechStats :248-249
+    d.sample_rate_f = sr_f;
+    return d;
+}
+
+// The VAD machine as an operator on a prepared series: every machine scans its own row of band minima.
+void vad_machine_scan(const fvad_vad_machine_config *cfgs, size_t n_machines, size_t sample_rate, size_t fft_size,
+                      const float *band_min, const float *ratio, size_t n_frames, size_t frames_per_launch,
+                      unsigned char *met, fvad_segment *segments, size_t max_segments, size_t *n_segments) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) throw Error(FVAD_ERR_NO_DEVICE, "no CUDA device: libfvad_cuda has no CPU path");
+    if (!cfgs || !n_machines || (n_frames && (!band_min || !ratio)) || !n_segments || (max_segments && !segments))
+        throw Error(FVAD_ERR_INVALID_ARGUMENT, "NULL argument");
+    const int M = (int)n_machines;
+    std::vector<ScanMachine> hm(n_machines);
+    int pitch = 0, fast = 1;
+    for (int m = 0; m < M; ++m) {
+        hm[(size_t)m] = derive_machine(cfgs[m], sample_rate, fft_size);
+        hm[(size_t)m].band = m;
+        pitch = std::max(pitch, hm[(size_t)m].n_long + hm[(size_t)m].n_short + hm[(size_t)m].n_ratio);
+        if (hm[(size_t)m].n_long < 2 * 256 + 2 || hm[(size_t)m].n_short + hm[(size_t)m].n_ratio > 64) fast = 0;
+    }
+    const size_t nf = std::max<size_t>(n_frames, 1), ms = std::max<size_t>(max_segments, 1);
+    DevBuf<ScanMachine> d_m; DevBuf<ScanState> d_st; DevBuf<double> d_rings; DevBuf<fvad_segment> d_seg;
+    DevBuf<float> d_band, d_ratio; DevBuf<unsigned char> d_met;
+    d_m.ensure(n_machines); d_st.ensure(n_machines); d_rings.ensure(n_machines * (size_t)pitch); d_seg.ensure(n_machines * ms);
+    d_band.ensure(n_machines * nf); d_ratio.ensure(nf); d_met.ensure(n_machines * nf);
+    FVAD_CUDA_CHECK(cudaMemcpy(d_m.p, hm.data(), hm.size() * sizeof(ScanMachine), cudaMemcpyHostToDevice));
+    if (n_frames) {
+        FVAD_CUDA_CHECK(cudaMemcpy(d_band.p, band_min, n_machines * n_frames * sizeof(float), cudaMemcpyHostToDevice));
+        FVAD_CUDA_CHECK(cudaMemcpy(d_ratio.p, ratio, n_frames * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    init_scan_kernel<<<(unsigned)M, 128>>>(d_st.p, d_rings.p, d_m.p, 1, M, pitch);
+    FVAD_LAUNCHED();
+    const size_t step = frames_per_launch ? frames_per_launch : nf;
+    for (size_t f0 = 0; f0 < n_frames; f0 += step) {
+        ScanArgs ca;
+        ca.band = d_band.p + f0; ca.ratio = d_ratio.p + f0; ca.machines = d_m.p; ca.states = d_st.p;
+        ca.rings = d_rings.p; ca.ring_pitch = pitch; ca.segments = d_seg.p; ca.max_segments = (int)max_segments;
+        ca.met = d_met.p + f0; ca.met_per_machine = 1; ca.S = 1; ca.M = M;
+        ca.n_frames = (int)std::min(step, n_frames - f0); ca.max_frames = (int)nf;
+        ca.first_frame = (long long)f0; ca.fft_size = (int)fft_size; ca.fast = fast;
+        launch_vadscan(ca, 0);
+    }
+    FVAD_CUDA_CHECK(cudaGetLastError());
+    std::vector<ScanState> hs(n_machines);
+    FVAD_CUDA_CHECK(cudaMemcpy(hs.data(), d_st.p, n_machines * sizeof(ScanState), cudaMemcpyDeviceToHost));
+    if (met && n_frames) FVAD_CUDA_CHECK(cudaMemcpy(met, d_met.p, n_machines * n_frames, cudaMemcpyDeviceToHost));
+    for (int m = 0; m < M; ++m) {
+        n_segments[m] = hs[(size_t)m].n_segments;
+        const size_t have = std::min<size_t>(hs[(size_t)m].n_segments, max_segments);
+        if (have) FVAD_CUDA_CHECK(cudaMemcpy(segments + (size_t)m * max_segments, d_seg.p + (size_t)m * max_segments,
+                                             have * sizeof(fvad_segment), cudaMemcpyDeviceToHost));
+    }
+}
+
 void Batch::init_machines(const fvad_config &cfg) {
     const fvad_vad_config &vc = cfg.vad_config;
     M_ = 1 + (int)(vc.alt_vad_machine_configs ? vc.n_alt_vad_machine_configs : 0);
@@ -62,24 +136,9 @@ void Batch::init_machines(const fvad_config &cfg) {
         for (size_t i = 0; i < lo.size(); ++i)
             if (lo[i] == md.bin_lo && hi[i] == md.bin_hi) b = (int)i;
         if (b < 0) { b = (int)lo.size(); lo.push_back(md.bin_lo); hi.push_back(md.bin_hi); }
-        ScanMachine &d = md.dev;
-        d.band = b;
-        // VADMachine.init, reference src/AudioPipeline/VADMachine.zig:75-106 (f32 products, truncation)
-        const float evals = sr_f / fft_f;
-        d.n_long = std::max<long long>(1, (long long)(evals * c.long_term_speech_avg_sec));
-        d.n_short = std::max<long long>(1, (long long)(evals * c.short_term_speech_avg_sec));
-        d.n_ratio = std::max<long long>(1, (long long)(evals * c.channel_vol_ratio_avg_sec));  // reference: no max(1); 0 would trap
-        d.has_init = c.has_initial_long_term_avg;
-        d.init_avg = c.initial_long_term_avg;
-        d.threshold_factor = (double)c.speech_threshold_factor;
-        d.ratio_threshold = (double)c.channel_vol_ratio_threshold;
-        // VADMachine.run :160-163, getOffsetRecording{Start,End} :312-325
-        d.min_to_open = (unsigned long long)(sr_f * c.min_consecutive_sec_to_open);
-        d.max_gap = (unsigned long long)(sr_f * c.max_speech_gap_sec);
-        d.start_margin = d.end_margin = (unsigned long long)(sr_f * 2);
-        d.min_duration_sec = c.min_vad_duration_sec;
-        d.frame_sec = fft_f / sr_f;  // trackSpeechStats :248-249
-        d.sample_rate_f = sr_f;
+        md.dev = derive_machine(c, sample_rate_, (size_t)fft_size_);
+        md.dev.band = b;
+        const ScanMachine &d = md.dev;
         machines_[(size_t)m] = md;
         ring_pitch_ = std::max(ring_pitch_, d.n_long + d.n_short + d.n_ratio);
         if (d.n_long < 2 * 256 + 2 || d.n_short + d.n_ratio > 64) scan_fast_ = 0;  // vadscan.cu fast-path limits

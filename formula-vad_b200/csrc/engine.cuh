@@ -129,6 +129,10 @@ private:
 };
 
 // eval.cu: one pair of lists (host pointers)
+ScanMachine derive_machine(const fvad_vad_machine_config &c, size_t sample_rate, size_t fft_size);
+void vad_machine_scan(const fvad_vad_machine_config *cfgs, size_t n_machines, size_t sample_rate, size_t fft_size,
+                      const float *band_min, const float *ratio, size_t n_frames, size_t frames_per_launch,
+                      unsigned char *met, fvad_segment *segments, size_t max_segments, size_t *n_segments);
 void evaluate_lists(const fvad_eval_segment *vad, size_t n_vad, const fvad_eval_segment *ref, size_t n_ref,
                     const fvad_eval_config &cfg, fvad_eval_stats *out);
 

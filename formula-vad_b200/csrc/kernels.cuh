@@ -90,6 +90,7 @@ struct ScanArgs {
     fvad_segment *segments;      // [S][M][max_segments]
     int max_segments;
     unsigned char *met;          // [S][max_frames] machine-0 decisions or nullptr
+    int met_per_machine = 0;     // 1: met is [S][M][max_frames], every machine writes its row
     int S, M, n_frames, max_frames;
     long long first_frame;       // absolute frame number of column 0
     int fft_size;

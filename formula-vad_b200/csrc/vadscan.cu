@@ -97,7 +97,8 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_kernel(ScanArgs a) {
     const float *__restrict__ band = a.band + ((size_t)mc.band * a.S + s) * a.max_frames;
     const float *__restrict__ ratio = a.ratio + (size_t)s * a.max_frames;
     fvad_segment *segs = a.segments + (size_t)t * a.max_segments;
-    unsigned char *met_out = (a.met && m == 0) ? a.met + (size_t)s * a.max_frames : nullptr;
+    unsigned char *met_out = !a.met ? nullptr : a.met_per_machine ? a.met + (size_t)t * a.max_frames
+                             : (m == 0 ? a.met + (size_t)s * a.max_frames : nullptr);
 
     for (int i0 = 0; i0 < a.n_frames; i0 += PF) {
         float eb[PF], rb[PF];
@@ -186,7 +187,8 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
     const float *__restrict__ band = a.band + ((size_t)mc.band * a.S + s) * a.max_frames;
     const float *__restrict__ ratio = a.ratio + (size_t)s * a.max_frames;
     fvad_segment *segs = a.segments + (size_t)t * a.max_segments;
-    unsigned char *met_out = (a.met && m == 0) ? a.met + (size_t)s * a.max_frames : nullptr;
+    unsigned char *met_out = !a.met ? nullptr : a.met_per_machine ? a.met + (size_t)t * a.max_frames
+                             : (m == 0 ? a.met + (size_t)s * a.max_frames : nullptr);
     const int hs = mc.n_short - 1, hr = mc.n_ratio - 1;
     for (int k = lane; k < hs; k += 32) x_s[k] = (float)ring_short[k];
     for (int k = lane; k < hr; k += 32) x_r[k] = (float)ring_ratio[k];

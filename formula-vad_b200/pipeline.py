@@ -276,6 +276,38 @@ class Evaluator:
         return _stats_dict(st)
 
 
+class VADMachine:
+    """Mirror of src/AudioPipeline/VADMachine.zig run over a whole series: `VADMachine(configs, sample_rate).scan(
+    band_min, ratio)`.  band_min is [n_machines][n_frames] (each machine's speech-band sum minimised over the
+    channels), ratio [n_frames].  Returns (met [n_machines][n_frames] uint8, [segments per machine])."""
+
+    def __init__(self, configs, sample_rate: int, fft_size: int = 1024, max_segments: int = 4096):
+        self.configs = list(configs) if isinstance(configs, (list, tuple)) else [configs]
+        self.sample_rate, self.fft_size, self.max_segments = sample_rate, fft_size, max_segments
+
+    def scan(self, band_min: np.ndarray, ratio: np.ndarray, frames_per_launch: int = 0):
+        M = len(self.configs)
+        band = np.ascontiguousarray(band_min, dtype=np.float32).reshape(M, -1)
+        rat = np.ascontiguousarray(ratio, dtype=np.float32).reshape(-1)
+        n = band.shape[1]
+        if rat.shape[0] != n:
+            raise ValueError("ratio must have one value per frame")
+        cfgs = (capi.VadMachineConfig * M)(*self.configs)
+        met = np.zeros((M, n), dtype=np.uint8)
+        segs = (capi.Segment * (M * self.max_segments))()
+        nseg = (C.c_size_t * M)()
+        check(capi.lib().fvad_vad_machine_scan(cfgs, M, self.sample_rate, self.fft_size, band.ctypes.data_as(capi.c_f32p),
+                                               rat.ctypes.data_as(capi.c_f32p), n,
+                                               frames_per_launch, met.ctypes.data_as(C.c_void_p), segs, self.max_segments, nseg))
+        out = []
+        for m in range(M):
+            k = min(int(nseg[m]), self.max_segments)
+            out.append([(segs[m * self.max_segments + i].sample_from, segs[m * self.max_segments + i].sample_to,
+                         segs[m * self.max_segments + i].avg_channel_vol_ratio, segs[m * self.max_segments + i].vad_met_sec)
+                        for i in range(k)])
+        return met, out
+
+
 class BatchPipeline:
     """n_streams independent AudioPipelines advanced in lock step on one GPU."""
     _h = None

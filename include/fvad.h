@@ -240,6 +240,21 @@ FVAD_API int fvad_evaluate(const fvad_eval_segment *vad, size_t n_vad, const fva
 FVAD_API int fvad_batch_evaluate(fvad_batch *b, const fvad_eval_segment *references, const size_t *reference_offsets,
                                  const fvad_eval_config *cfg, fvad_eval_stats *out);
 
+/* ------------------------------------------------------------------------------------------
+ * VADMachine as an operator -- replaces VADMachine.init + VADMachine.run (src/AudioPipeline/VADMachine.zig:75-106,
+ * 138-325) over a prepared series, for n_machines configurations at once (one warp each).  The inputs are what
+ * run() derives from a VADPipeline.Result before it touches any state: band_min[m][f] is machine m's speech-band
+ * sum minimised over the channels (:141-158), ratio[f] the frame's channel volume ratio (:173).  Frame f starts at
+ * sample f * fft_size.  frames_per_launch > 0 cuts the series into launches of that many frames (the state is
+ * carried in device memory in between, as the pipeline does from span to span); 0 = one launch.
+ * met: [n_machines][n_frames] threshold decisions or NULL; segments: [n_machines][max_segments];
+ * n_segments[m] counts every completed segment, also those beyond max_segments.  Host pointers.
+ * ---------------------------------------------------------------------------------------- */
+FVAD_API int fvad_vad_machine_scan(const fvad_vad_machine_config *cfgs, size_t n_machines, size_t sample_rate,
+                                   size_t fft_size, const float *band_min, const float *ratio, size_t n_frames,
+                                   size_t frames_per_launch, uint8_t *met, fvad_segment *segments, size_t max_segments,
+                                   size_t *n_segments);
+
 #ifdef __cplusplus
 }
 #endif
