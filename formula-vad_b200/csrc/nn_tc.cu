@@ -76,6 +76,7 @@ struct Layer {  // one dense layer prepared for launch_tc_gemm
     DevBuf<__half> img, img2;
     DevBuf<float> bias;
     int K = 0, Nc = 0, n_valid = 0, n_tiles = 0;
+    int a_tmem = 0;  // GemmArgs::a_tmem for this layer (the N-tiles were cut for it)
     int nt_size[tc::kMaxNTiles] = {}, nt_col[tc::kMaxNTiles] = {};
     unsigned nt_off[tc::kMaxNTiles] = {};
 };
@@ -141,6 +142,11 @@ public:
         if (const char *e = getenv("FVAD_NN_TIMING")) timing_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_GEMM_PAIR")) gemm_pair_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_FUSED_PACK")) fused_pack_ = atoi(e) != 0;
+        if (const char *e = getenv("FVAD_GEMM_TS")) gemm_ts_ = atoi(e) != 0;
+        if (gemm_pair_) gemm_ts_ = false;
+        // N-tiles: with the A tile in TMEM (K/2 columns) the two accumulators share what is left of the 512 columns
+        const bool ts = gemm_ts_;
+        using T = std::vector<int>;
         const int H = 400;
         // gate-row permutation: p = 48c + 16g + u  <-  g*400 + 16c + u
         std::vector<int> perm(3 * H);
@@ -152,7 +158,8 @@ public:
             // xp bias: Wb + Rb for z and r; Wb alone for n (Rb_n is applied inside r*(.), nn_tc_gru.cu)
             std::vector<float> b(3 * H);
             for (int i = 0; i < 3 * H; ++i) b[(size_t)i] = w.gru_Wb[l][(size_t)i] + (i < 2 * H ? w.gru_Rb[l][(size_t)i] : 0.0f);
-            build_layer(gW_[l], w.gru_W[l].data(), b.data(), perm.data(), 3 * H, H, H, {240, 240, 240, 240, 240});
+            build_layer(gW_[l], w.gru_W[l].data(), b.data(), perm.data(), 3 * H, H, H,
+                        ts ? T{144, 144, 144, 144, 144, 144, 144, 144, 48} : T{240, 240, 240, 240, 240});
             // R: 25 chunk images of 48 rows = one "layer" with 25 N-tiles of 48
             Layer tmp;
             std::vector<__half> img((size_t)3 * H * H);
@@ -177,9 +184,13 @@ public:
             gRbn_[l].ensure((size_t)H);
             FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
         }
-        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, {208, 208, 192});
-        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, {208, 208, 192});
-        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, {176});
+        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, T{208, 208, 192});
+        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, T{208, 208, 192});
+        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, ts ? T{96, 80} : T{176});
+        // A in TMEM caps the N-tile at (512 - K/2)/2 columns: 144 at K = 400, 96 at K = 608.  Measured per 20 stream-hours:
+        // fc1 2.12 -> 1.75 ms, W1/W2 8.6 -> 7.5, fc4 3.43 -> 3.2; fc2 unchanged (4.0) and fc3 (K = 608, N-tile 96) 7.3 -> 8.8,
+        // so those two keep A in shared memory with N-tiles of 208
+        fc1_.a_tmem = gW_[0].a_tmem = gW_[1].a_tmem = fc4_.a_tmem = ts ? 1 : 0;
     }
     const char *name() const override { return "tcgen05-f16"; }
 
@@ -297,6 +308,7 @@ private:
     bool pair_ = false;
     bool fused_pack_ = false;  // FVAD_FUSED_PACK=1: the STFT writes the fp16 input tiles itself -- measured slower (its 16-byte
                                // pieces land 2 KB apart and cost the STFT +75 %, more than the pack kernel's 5 ms), kept for A/B
+    bool gemm_ts_ = true;     // A tile in TMEM (FVAD_GEMM_TS=0: resident in shared memory, the first design)
     bool gemm_pair_ = false;  // CTA-pair GEMM (FVAD_GEMM_PAIR=1): parity-green but 50 % slower than the one-CTA kernel, kept for A/B
 
     void gru(int l, __half *hout, int Q, int t_store_min, cudaStream_t s) {
@@ -323,6 +335,7 @@ private:
         g.K = L.K; g.Nc = L.Nc; g.n_valid = L.n_valid; g.n_tiles = L.n_tiles;
         for (int j = 0; j < L.n_tiles; ++j) { g.nt_size[j] = L.nt_size[j]; g.nt_col[j] = L.nt_col[j]; g.nt_off[j] = L.nt_off[j]; }
         if (const char *e = getenv("FVAD_GEMM_DBG")) g.dbg = atoi(e);
+        g.a_tmem = L.a_tmem;
         g.mt_count = Q * T; g.T = T; g.A_q = A_q; g.A_t0 = A_t0; g.C_q = C_q; g.C_t0 = C_t0; g.act = act;
         return g;
     }

@@ -8,7 +8,7 @@ namespace fvad {
 namespace tc {
 
 constexpr int kTileM = 128;            // rows (sequences) per M-tile = TMEM lanes
-constexpr int kMaxNTiles = 8;
+constexpr int kMaxNTiles = 12;
 
 // bytes of one activation tile of `cols` columns (cols % 16 == 0) in the core-matrix tiled layout
 __host__ __device__ constexpr size_t tile_bytes(int cols) { return (size_t)kTileM * cols * 2; }
@@ -37,6 +37,8 @@ struct GemmArgs {
     int act;       // 0 none, 1 relu, 2 sigmoid
     int out_mode;
     unsigned long long *trace;  // debug (FVAD_GEMM_TRACE): CTA 0 logs clock64 for its first 4 M-tiles, nullptr otherwise
+    int a_tmem;    // 1: the A tile lives in TMEM (tcgen05.cp + A-from-TMEM MMAs), all shared memory is weight ring; needs
+                   //    K/2 + 2*max(nt_size) <= 512 TMEM columns
     int dbg;       // experiments only (FVAD_GEMM_DBG): bit 0 epilogue does no work, bit 1 producer copies nothing
     int seq0, n_seq, Kchunks;  // scatter: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
 };

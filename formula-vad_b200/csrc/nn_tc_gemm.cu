@@ -22,8 +22,8 @@ namespace {
 // first N-tile runs) and stays resident for all N-tiles, so L2 traffic per M-tile is A + the whole
 // weight matrix: 128 flop per byte, the same intensity as the GRU kernel's R stream.
 constexpr int kMaxSlabs = 40;
-constexpr int kMaxStages = 8;
-constexpr int kGemmThreads = 256;
+constexpr int kMaxStages = 16;
+constexpr int kGemmThreads = 384;  // 4 control warps, 4 epilogue warps, 4 A-stager warps (TS only)
 // 214 KB, not the full 227: the VAD scan of the previous span runs concurrently on its own stream (one warp and
 // ~11 KB of shared memory per stream); a persistent GEMM CTA that takes a whole SM's shared memory cannot start
 // on the SMs the scan occupies, and with a static tile assignment the late CTAs stretch the kernel by ~60 %
@@ -32,7 +32,7 @@ constexpr int kSmemTotal = 214 * 1024;
 
 // timeline probe (CTA 0, first 4 M-tiles): [kind][mtile][ntile][slab], kinds: 0 producer B issued, 1 MMA full ok,
 // 2 MMA issued, 3 epilogue acc_full ok (slab 0) / done (slab 1), 4 MMA acc_empty ok (slab 0)
-#define GEMM_TRACE(kind, im, j, sl) do { if (a.trace && blockIdx.x == 0 && (im) < 4) \
+#define GEMM_TRACE(kind, im, j, sl) do { if (a.trace && blockIdx.x == 0 && (im) < 4 && (j) < 8) \
     a.trace[(((kind) * 4 + (im)) * 8 + (j)) * 32 + (sl)] = (unsigned long long)clock64(); } while (0)
 
 struct GemmShared {
@@ -42,11 +42,20 @@ struct GemmShared {
 
 struct GemmPlan {  // host-computed shared-memory plan
     int KS, n_slabs, n_stages, stage_bytes, a_bytes, bias_off, tr_off, sh_off, smem_bytes;
+    int acc_cols;  // TMEM columns between the two accumulators
 };
 
 // ACT: 0 none, 1 relu, 2 sigmoid.  OUT: 0 fp16 tiles for the next layer, 1 f32 gains rows (coalesced through a
 // per-warp shared-memory transpose).
-template <int ACT, int OUT>
+//
+// TS = true (GemmArgs::a_tmem): the A tile goes to TENSOR MEMORY instead.  Its K slabs travel through the ring like
+// weight slabs; four stager warps (thread = row) move each from its ring stage into TMEM with tcgen05.st, slab by
+// slab as the previous M-tile's last N-tile releases the columns (a_empty[sl] / a_full[sl]), and every MMA takes A
+// from TMEM.  (tcgen05.cp from the MMA thread does the same copy without the extra warps but takes ~250 cycles per
+// 128x32-byte piece, 5-7 k cycles per M-tile with the tensor pipe idle -- measured, then replaced.)  That frees A's 100 KB for the weight ring -- the SS form's timeline
+// (profiles/r01_gemm_timeline.txt) is bound by ring bytes in flight, three 30 KB stages against a 1 400-2 400
+// cycle L2 latency -- and halves the shared-memory read traffic per MMA.  TMEM columns: [acc 0 | acc 1 | A (K/2)].
+template <int ACT, int OUT, bool TS>
 __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs a, const GemmPlan pl) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t *sA = smem, *sB = smem + pl.a_bytes;
@@ -85,12 +94,22 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
             for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
                 const int q = mt / a.T, t = mt % a.T;
                 const uint8_t *At = reinterpret_cast<const uint8_t *>(a.A) + (size_t)(q * a.A_q + t + a.A_t0) * a_tile_bytes;
+                if (TS) {  // this M-tile's A slabs, one ring stage each
+                    for (int sl = 0; sl < n_slabs; ++sl) {
+                        const int k0 = sl * KS, kw = min(KS, a.K - k0);
+                        mbar_wait(&sh->empty[st], ph ^ 1);
+                        const uint32_t ab = (uint32_t)(kw / 8) * (kTileM * 16);
+                        mbar_expect_tx(&sh->full[st], ab);
+                        bulk_g2s(sB + (size_t)st * pl.stage_bytes, At + (size_t)(k0 / 8) * (kTileM * 16), ab, &sh->full[st]);
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
+                    }
+                }
                 for (int j = 0; j < a.n_tiles; ++j) {
                     const int NT = a.nt_size[j];
                     const uint8_t *Bt = reinterpret_cast<const uint8_t *>(a.B) + a.nt_off[j];
                     for (int sl = 0; sl < n_slabs; ++sl, ++it) {
                         const int k0 = sl * KS, kw = min(KS, a.K - k0);
-                        if (j == 0) {  // this M-tile's A slab (slot freed by the previous M-tile's last N-tile)
+                        if (!TS && j == 0) {  // this M-tile's A slab (slot freed by the previous M-tile's last N-tile)
                             mbar_wait(&sh->a_empty[sl], (im & 1) ^ 1);
                             const uint32_t ab = (uint32_t)(kw / 8) * (kTileM * 16);
                             mbar_expect_tx(&sh->a_full[sl], ab);
@@ -116,7 +135,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
             // descriptors as (lo, hi): the K loop advances lo by immediates (tc_dev.cuh, mma_ss_lohi)
             const uint64_t ad0 = make_smem_desc(smem_u32(sA), kTileM * 16, 128);
             const uint32_t alo0 = (uint32_t)ad0, ahi = (uint32_t)(ad0 >> 32);
+            const uint32_t tA = tmem + 2u * (uint32_t)pl.acc_cols;  // TS: A image, 8 columns per K-step of 16
             for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
+                if (TS) {  // the stager warps consume this M-tile's A stages
+                    st += (uint32_t)n_slabs;
+                    while (st >= (uint32_t)n_stages) { st -= (uint32_t)n_stages; ph ^= 1; }
+                }
                 for (int j = 0; j < a.n_tiles; ++j, ++work) {
                     const int NT = a.nt_size[j];
                     const uint32_t buf = work & 1;
@@ -124,7 +148,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                     tc_fence_after();
                     GEMM_TRACE(4, im, j, 0);
                     const uint32_t idesc = make_idesc_f16(kTileM, NT);
-                    const uint32_t d = tmem + buf * 256;
+                    const uint32_t d = tmem + buf * (uint32_t)pl.acc_cols;
                     const bool last_n = (j == a.n_tiles - 1);
                     const uint32_t bstep = 2u * (uint32_t)NT;  // one K-step of B = 2 core columns = 2*NT*16 bytes
                     for (int sl = 0; sl < n_slabs; ++sl) {
@@ -136,18 +160,63 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                         const uint64_t bd0 = make_smem_desc(smem_u32(sB + (size_t)st * pl.stage_bytes), NT * 16, 128);
                         const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
                         const uint32_t alo = alo0 + (uint32_t)(k0 / 8) * (kTileM * 16 / 16);
-                        if (sl == 0) mma_ss_lohi<false>(d, alo, ahi, blo, bhi, idesc);
-                        else mma_ss_lohi<true>(d, alo, ahi, blo, bhi, idesc);
+                        if (TS) {
+                            const uint32_t ta = tA + (uint32_t)(k0 / 16) * 8u;
+                            if (sl == 0) mma_ts_lohi<false>(d, ta, blo, bhi, idesc);
+                            else mma_ts_lohi<true>(d, ta, blo, bhi, idesc);
 #pragma unroll
-                        for (int kk = 1; kk < 4; ++kk)
-                            if (kk < nk) mma_ss_lohi<true>(d, alo + kk * (2 * kTileM * 16 / 16), ahi, blo + kk * bstep, bhi, idesc);
+                            for (int kk = 1; kk < 8; ++kk)
+                                if (kk < nk) mma_ts_lohi<true>(d, ta + kk * 8u, blo + kk * bstep, bhi, idesc);
+                        } else {
+                            if (sl == 0) mma_ss_lohi<false>(d, alo, ahi, blo, bhi, idesc);
+                            else mma_ss_lohi<true>(d, alo, ahi, blo, bhi, idesc);
+#pragma unroll
+                            for (int kk = 1; kk < 4; ++kk)
+                                if (kk < nk) mma_ss_lohi<true>(d, alo + kk * (2 * kTileM * 16 / 16), ahi, blo + kk * bstep, bhi, idesc);
+                        }
                         mma_commit(&sh->empty[st]);               // B stage free once these MMAs have read it
-                        if (last_n) mma_commit(&sh->a_empty[sl]); // A slab free for the next M-tile
+                        if (last_n) mma_commit(&sh->a_empty[sl]); // A slab (smem, or its TMEM columns) free for the next M-tile
                         GEMM_TRACE(2, im, j, sl);
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                     mma_commit(&sh->acc_full[buf]);
+                    GEMM_TRACE(4, im, j, 1);
                 }
+            }
+        }
+    } else if (warp >= 8) {
+        // ===== A stagers (TS): ring stage -> TMEM, thread = row (lane quadrant = warp % 4) =====
+        if (TS) {
+            const int row = (warp & 3) * 32 + lane;
+            const uint32_t tA = tmem + 2u * (uint32_t)pl.acc_cols + ((uint32_t)((warp & 3) * 32) << 16);
+            uint32_t st = 0, ph = 0, im = 0;
+            for (int mt = blockIdx.x; mt < a.mt_count; mt += gridDim.x, ++im) {
+                for (int sl = 0; sl < n_slabs; ++sl) {
+                    const int k0 = sl * KS, nk = min(KS, a.K - k0) / 16;
+                    mbar_wait(&sh->a_empty[sl], (im & 1) ^ 1);  // the previous M-tile's MMAs over these columns are done
+                    mbar_wait(&sh->full[st], ph);
+                    tc_fence_after();
+                    const uint8_t *src = sB + (size_t)st * pl.stage_bytes + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        if (kk < nk) {
+                            const uint4 lo = *reinterpret_cast<const uint4 *>(src + (size_t)(2 * kk) * (kTileM * 16));
+                            const uint4 hi = *reinterpret_cast<const uint4 *>(src + (size_t)(2 * kk + 1) * (kTileM * 16));
+                            const uint32_t r[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+                            tmem_st8(tA + (uint32_t)(k0 / 16 + kk) * 8u, r);
+                        }
+                    }
+                    tmem_wait_st();
+                    tc_fence_before();
+                    bar_sync(1, 128);
+                    if (warp == 8 && lane == 0) {
+                        mbar_arrive(&sh->empty[st]);
+                        mbar_arrive(&sh->a_full[sl]);
+                    }
+                    if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
+                }
+                st += (uint32_t)(a.n_tiles * n_slabs);
+                while (st >= (uint32_t)n_stages) { st -= (uint32_t)n_stages; ph ^= 1; }
             }
         }
     } else if (warp >= 4) {
@@ -192,8 +261,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                 const uint32_t buf = work & 1;
                 mbar_wait(&sh->acc_full[buf], (work >> 1) & 1);
                 tc_fence_after();
-                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 0);
-                const uint32_t tbase = tmem + buf * 256 + ((uint32_t)(wq * 32) << 16);
+                if (warp == 4 && lane == 0) GEMM_TRACE(3, im, j, 0);
+                const uint32_t tbase = tmem + buf * (uint32_t)pl.acc_cols + ((uint32_t)(wq * 32) << 16);
                 for (int c = 0; c < ((a.dbg & 1) ? 0 : NT); c += 32) {
                     uint32_t r[32];
                     const bool full32 = c + 32 <= NT;  // N-tiles are multiples of 16
@@ -241,7 +310,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 1);
+                if (warp == 4 && lane == 0) GEMM_TRACE(3, im, j, 1);
                 if (lane == 0) mbar_arrive(&sh->acc_empty[buf]);
             }
         }
@@ -253,14 +322,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const GemmArgs
 
 }  // namespace
 
-template <int ACT, int OUT>
-static void launch_variant(const GemmArgs &a, const GemmPlan &pl, int grid, cudaStream_t s) {
+template <int ACT, int OUT, bool TS>
+static void launch_variant2(const GemmArgs &a, const GemmPlan &pl, int grid, cudaStream_t s) {
     static bool attr = false;
     if (!attr) {
-        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<ACT, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<ACT, OUT, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
         attr = true;
     }
-    tc_gemm_kernel<ACT, OUT><<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
+    tc_gemm_kernel<ACT, OUT, TS><<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
+}
+template <int ACT, int OUT>
+static void launch_variant(const GemmArgs &a, const GemmPlan &pl, int grid, cudaStream_t s) {
+    if (a.a_tmem) launch_variant2<ACT, OUT, true>(a, pl, grid, s);
+    else launch_variant2<ACT, OUT, false>(a, pl, grid, s);
 }
 
 void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
@@ -268,13 +342,17 @@ void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     GemmPlan pl;
     int nt_max = 0;
     for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
-    pl.a_bytes = a.K * 256;  // K/8 core columns x 2048 B
+    pl.a_bytes = a.a_tmem ? 0 : a.K * 256;  // K/8 core columns x 2048 B
+    pl.acc_cols = a.a_tmem ? nt_max : 256;
+    if (a.a_tmem && (a.K / 2 + 2 * nt_max > 512 || a.K % 16))
+        throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: A tile + two accumulators exceed the 512 TMEM columns");
     const int tr_bytes = a.out_mode == 1 ? 4 * 32 * 33 * 4 : 0;
     static_assert(sizeof(GemmShared) <= 1024, "barrier block");
     const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 1024;
-    pl.KS = 64;
+    pl.KS = a.a_tmem ? 128 : 64;  // (the SS issue loop is unrolled for 4 K-steps, the TS one for 8)
+    if (a.a_tmem && (a.dbg & 8)) pl.KS = 64;
     for (;;) {
-        pl.stage_bytes = nt_max * pl.KS * 2;
+        pl.stage_bytes = (a.a_tmem && nt_max < kTileM ? kTileM : nt_max) * pl.KS * 2;  // (a stage also carries A slabs when a_tmem)
         pl.n_stages = (kSmemTotal - pl.a_bytes - fixed) / pl.stage_bytes;
         if (pl.n_stages >= 3 || pl.KS == 16) break;  // fewer, larger stages: the per-stage barrier round trip costs the issuing thread more than the shorter ring
         pl.KS /= 2;

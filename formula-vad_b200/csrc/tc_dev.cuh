@@ -186,6 +186,18 @@ __device__ __forceinline__ void mma_ss_lohi(uint32_t d_tmem, uint32_t a_lo, uint
         : "memory");
 }
 
+// shared memory -> TMEM: 128 rows x 32 bytes (two K-adjacent 8x16-byte core matrices per 8 rows, addressed by the
+// same K-major descriptor an A operand uses) land in lanes 0..127 x 8 columns -- exactly the A-from-TMEM image of one
+// K = 16 step.  Asynchronous, and pipelined in issue order with this thread's tcgen05.mma (no wait in between).
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint32_t d_lo, uint32_t d_hi) {
+    asm volatile(
+        "{\n\t.reg .b64 sd;\n\t"
+        "mov.b64 sd, {%1, %2};\n\t"
+        "tcgen05.cp.cta_group::1.128x256b [%0], sd;\n\t}\n" ::"r"(taddr),
+        "r"(d_lo), "r"(d_hi)
+        : "memory");
+}
+
 // all MMAs issued so far by this thread arrive (once) on `bar` when they complete
 __device__ __forceinline__ void mma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");

@@ -10,7 +10,7 @@ for j in range(8):
     if t[4, im, j, 0] == 0:
         break
     r = lambda k, sl: t[k, im, j, sl] - base
-    print(f"N-tile {j}: accEmptyOK {r(4,0):7d} | epi start {r(3,0):7d} done {r(3,1):7d}")
+    print(f"N-tile {j}: accEmptyOK {r(4,0):7d} | committed {r(4,1):7d} | epi start {r(3,0):7d} done {r(3,1):7d}")
     print("   slab: prodIssued / mmaFullOK / mmaIssued")
     for sl in range(nsl):
         print(f"   {sl:2d}  {r(0,sl):7d} {r(1,sl):7d} {r(2,sl):7d}")
