@@ -229,6 +229,7 @@ Batch::Batch(size_t n_streams, const fvad_config &cfg, const HostWeights *weight
         tail_[i].ensure((size_t)SC_ * kHop); tail_[i].zero(stream_);
     }
     ctx_carry_.ensure((size_t)SC_ * kCtx * kBins); ctx_carry_.zero(stream_);  // NSNet2.zig:79 context rows start at 0.0
+    ctx16_carry_.ensure((size_t)SC_ * kCtx * 88); ctx16_carry_.zero(stream_);
     ylook_carry_.ensure((size_t)SC_ * kYLook); ylook_carry_.zero(stream_);
     sumsq_carry_.ensure((size_t)SC_); sumsq_carry_.zero(stream_);
     pend_.ensure((size_t)SC_ * chunk_);
@@ -263,7 +264,11 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
     const size_t ypitch = (size_t)kYLook + (size_t)kChunk16 * K;
     const bool full = !opt_.stft_only;
     spec_.ensure((size_t)SC_ * rows * kBins);
-    feat_.ensure((size_t)SC_ * frow * kBins);
+    // feature rows: fp16 for a backend that reads them so, f32 for the others and for the taps
+    const bool want16 = nn_ && full && !forced_.p && nn_->wants_feat16();
+    const bool want32 = !want16 || opt_.keep_taps;
+    if (want32) feat_.ensure((size_t)SC_ * frow * kBins);
+    if (want16) feat16_.ensure((size_t)SC_ * frow * 88);
     sumsq_.ensure((size_t)SC_ * (K + 1));
     if (full) {
         gains_.ensure((size_t)SC_ * rows * kBins);
@@ -284,12 +289,13 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
     StftArgs sa;
     sa.x = d_x; sa.x_offset = x_offset;
     sa.halo_in = halo_[parity_].p; sa.halo_out = halo_[parity_ ^ 1].p;
-    sa.spec = spec_.p; sa.feat = feat_.p; sa.sumsq = sumsq_.p;
+    sa.spec = spec_.p; sa.feat = want32 ? feat_.p : nullptr; sa.sumsq = sumsq_.p;
     sa.K = K; sa.SC = SC_; sa.D = D_;
-    sa.nn_tiles = (nn_ && full && !forced_.p) ? nn_->input_tiles(SC_, K) : nullptr;
+    sa.feat16 = want16 ? feat16_.p : nullptr;
     launch_stft(sa, tables_, s);
     // 4 context feature rows carried from the previous span (NSNet2.zig:188-203)
-    launch_copy_rows(feat_.p, ctx_carry_.p, frow * kBins, (size_t)kCtx * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
+    if (want32) launch_copy_rows(feat_.p, ctx_carry_.p, frow * kBins, (size_t)kCtx * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
+    if (want16) launch_copy_rows(feat16_.p, ctx16_carry_.p, frow * 88, (size_t)kCtx * 88, (size_t)kCtx * 88, (size_t)SC_, s);
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[1], s));
 
     const uint64_t span_start = processed_;
@@ -303,7 +309,7 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
             launch_copy_rows(gains_.p, forced_.p + f0 * kBins, rows * kBins, opt_.forced_gain_frames * kBins, rows * kBins, (size_t)SC_, s);
             if (pscan_.valid) issue_scan(nullptr);
         } else {
-            NnSpan ns{feat_.p, gains_.p, SC_, K, ctx_carry_.p, sa.nn_tiles != nullptr};
+            NnSpan ns{want32 ? feat_.p : nullptr, gains_.p, SC_, K, want16 ? feat16_.p : nullptr};
             // The previous span's VAD scan starts once this span's recurrent layers are queued: their epilogue
             // warps are issue-bound, and a scan warp sharing an SM sub-partition with them stretched the whole
             // GRU launch by a third, while the GEMMs and the spectral kernels that follow do not notice it.
@@ -386,7 +392,8 @@ void Batch::process_span(const float *const *d_x, size_t x_offset, int K) {
     }
 
     // ---- carries for the next span ----
-    launch_copy_rows(ctx_carry_.p, feat_.p + rows * kBins, (size_t)kCtx * kBins, frow * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
+    if (want32) launch_copy_rows(ctx_carry_.p, feat_.p + rows * kBins, (size_t)kCtx * kBins, frow * kBins, (size_t)kCtx * kBins, (size_t)SC_, s);
+    if (want16) launch_copy_rows(ctx16_carry_.p, feat16_.p + rows * 88, (size_t)kCtx * 88, frow * 88, (size_t)kCtx * 88, (size_t)SC_, s);
     if (full) {
         launch_copy_rows(ylook_carry_.p, y16_.p + ypitch - kYLook, kYLook, ypitch, kYLook, (size_t)SC_, s);
         launch_copy_rows(sumsq_carry_.p, sumsq_.p + K, 1, (size_t)K + 1, 1, (size_t)SC_, s);

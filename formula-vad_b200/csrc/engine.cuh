@@ -93,6 +93,7 @@ private:
     size_t stage_pitch_ = 0;
     DevBuf<float> halo_[2], tail_[2];          // [SC][160]
     DevBuf<float> ctx_carry_, ylook_carry_, sumsq_carry_;
+    DevBuf<float> feat16_, ctx16_carry_;  // fp16 feature rows [SC][4+50K][176] and their 4-row carry, held as 88 floats per row
     DevBuf<fvad_complex> spec_;
     DevBuf<float> feat_, gains_, y16_, sumsq_, band_[2], ratio_[2];
     DevBuf<unsigned char> met_[2];

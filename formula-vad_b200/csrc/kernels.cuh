@@ -25,7 +25,8 @@ struct StftArgs {
     fvad_complex *spec;     // [SC][50K][161] or nullptr
     float *feat;            // [SC][4+50K][161]; rows 0..3 are the context carried by the caller
     float *sumsq;           // [SC][1+K]; this kernel fills slots 1..K
-    void *nn_tiles;         // optional: the tensor-core backend's fp16 input tiles [q][54] of 128 sequences x 176 columns
+    void *feat16;           // optional: the same feature rows as fp16, [SC][4+50K][176] (bins 161..175 zero): what the
+                            // tensor-core backend reads; `feat` may then be nullptr (no f32 rows written)
                             // (core-matrix tiled, nn_tc.cuh); each frame is written as row f+4 of its own sequence and,
                             // for f >= 46, as context row f-46 of the next chunk's sequence (NSNet2.zig:188-203)
     int K, SC, D;

@@ -22,11 +22,10 @@ struct HostWeights {
 // rows are feat[sc][50j .. 50j+53] (overlapping windows: rows 50j..50j+3 are the 4 context frames)
 // and whose output rows 4..53 land in gains[sc][50j .. 50j+49].
 struct NnSpan {
-    const float *feat;  // [SC][4+50K][161]
+    const float *feat;  // [SC][4+50K][161], or nullptr when the backend wants_feat16() and nothing else needs the f32 rows
     float *gains;       // [SC][50K][161]
     int SC, K;
-    const float *ctx;   // [SC][4][161] context rows of each stream-channel's first chunk (only read when tiles_ready)
-    bool tiles_ready;   // the STFT already wrote the backend's input tiles (input_tiles()) for rows it owns
+    const void *feat16; // the same rows as fp16 [SC][4+50K][176], or nullptr (only a backend with wants_feat16() gets them)
     cudaEvent_t after_rnn = nullptr;  // recorded on the stream once the span's last recurrent launch is queued (or at the
                                       // end of forward): the engine starts the previous span's VAD scan there
 };
@@ -36,9 +35,7 @@ public:
     virtual ~NnBackend() = default;
     virtual void forward(const NnSpan &span, cudaStream_t s) = 0;
     virtual const char *name() const = 0;
-    // tensor-core backend: device buffer the STFT may fill directly with fp16 input tiles for a span of SC x K
-    // sequences (nullptr: the backend reads the f32 feature rows itself)
-    virtual void *input_tiles(int SC, int K) { (void)SC; (void)K; return nullptr; }
+    virtual bool wants_feat16() const { return false; }  // reads NnSpan::feat16 instead of NnSpan::feat
     // CUDA-event ms and launch count per layer kernel {pack, fc1, W1, gru1, W2, gru2, fc2, fc3, fc4} since the last call
     virtual void take_layer_ms(double *ms9, unsigned *launches9) { for (int i = 0; i < 9; ++i) { ms9[i] = 0; launches9[i] = 0; } }
 };

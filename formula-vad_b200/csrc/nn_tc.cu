@@ -18,24 +18,21 @@ namespace tc {
 
 // ---- pack kernel: features f32 -> fp16 tiles -------------------------------------------------
 __global__ void __launch_bounds__(256) tc_pack_kernel(const PackArgs a) {
-    // one CTA per (q, t) tile: 128 rows x 176 columns.  A warp reads whole feature rows (161 consecutive floats,
-    // coalesced) and drops them as halves into a shared-memory image of the tile; the image then leaves with
-    // 16-byte stores in tile order, so both directions move full sectors.
+    // one CTA per (q, t) tile: 128 rows x 176 columns.  Row r of the tile is row 50j + t of its stream-channel's
+    // fp16 feature rows (352 contiguous bytes): a warp fetches a row as 22 16-byte pieces and drops each into its
+    // core column of a shared-memory image of the tile; the image then leaves with 16-byte stores in tile order.
     __shared__ __align__(16) uint8_t img[kTileM * 176 * 2];
     const int q = blockIdx.x / kSteps, t = blockIdx.x % kSteps;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int row = warp; row < kTileM; row += 8) {
         const int g = a.seq0 + q * kTileM + row;
-        const bool ok = g < a.n_seq;
-        const int sc = ok ? g / a.Kchunks : 0, j = ok ? g % a.Kchunks : 0;
-        const float *src = a.feat + ((size_t)sc * (kCtx + kFrames * a.Kchunks) + (size_t)kFrames * j + t) * kBins;
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            const int k = lane + 32 * i;
-            if (k < 176) {
-                const float v = (ok && k < kBins) ? __ldg(src + k) : 0.0f;
-                *reinterpret_cast<__half *>(img + tiled_off(row, k, kTileM)) = __float2half_rn(v);
+        if (lane < 22) {
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (g < a.n_seq) {
+                const int sc = g / a.Kchunks, j = g % a.Kchunks;
+                v = __ldg(reinterpret_cast<const uint4 *>(a.feat16 + ((size_t)sc * (kCtx + kFrames * a.Kchunks) + (size_t)kFrames * j + t) * 176) + lane);
             }
+            *reinterpret_cast<uint4 *>(img + (size_t)lane * (kTileM * 16) + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16) = v;
         }
     }
     __syncthreads();
@@ -47,21 +44,6 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(const PackArgs a) {
 void launch_tc_pack(const PackArgs &a, cudaStream_t s) {
     if (a.Q <= 0) return;
     tc_pack_kernel<<<(unsigned)(a.Q * kSteps), 256, 0, s>>>(a);
-    FVAD_LAUNCHED();
-    FVAD_CUDA_CHECK(cudaGetLastError());
-}
-
-// context rows t = 0..3 of every stream-channel's first sequence of the span (f32 carry [SC][4][161] -> tiles)
-__global__ void tc_ctx_pack_kernel(const float *ctx, __half *A0, int SC, int K) {
-    const int sc = blockIdx.x / kCtx, t = blockIdx.x % kCtx;
-    const int g = sc * K;
-    uint8_t *tile = reinterpret_cast<uint8_t *>(A0) + ((size_t)(g >> 7) * kSteps + t) * tile_bytes(176);
-    for (int k = threadIdx.x; k < kBins; k += blockDim.x)
-        *reinterpret_cast<__half *>(tile + tiled_off(g & 127, k, kTileM)) = __float2half_rn(ctx[((size_t)sc * kCtx + t) * kBins + k]);
-}
-
-void launch_tc_ctx_pack(const float *ctx, __half *A0, int SC, int K, cudaStream_t s) {
-    tc_ctx_pack_kernel<<<(unsigned)(SC * kCtx), 192, 0, s>>>(ctx, A0, SC, K);
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
 }
@@ -141,7 +123,6 @@ public:
         if (const char *e = getenv("FVAD_GRU_PAIR")) pair_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_NN_TIMING")) timing_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_GEMM_PAIR")) gemm_pair_ = atoi(e) != 0;
-        if (const char *e = getenv("FVAD_FUSED_PACK")) fused_pack_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_GEMM_TS")) gemm_ts_ = atoi(e) != 0;
         if (gemm_pair_) gemm_ts_ = false;
         // N-tiles: with the A tile in TMEM (K/2 columns) the two accumulators share what is left of the 512 columns
@@ -194,24 +175,14 @@ public:
     }
     const char *name() const override { return "tcgen05-f16"; }
 
-    // the STFT writes the fp16 input tiles of a whole span itself (fused pack); pad rows/columns stay zero
-    void *input_tiles(int SC, int K) override {
-        if (!fused_pack_) return nullptr;
-        const size_t q_total = ((size_t)SC * K + tc::kTileM - 1) / tc::kTileM;
-        const size_t need = q_total * kSteps * tc::tile_bytes(176) / 2;
-        if (need > a0_.n) {
-            a0_.ensure(need);
-            FVAD_CUDA_CHECK(cudaMemset(a0_.p, 0, a0_.n * sizeof(__half)));
-        }
-        return a0_.p;
-    }
+    bool wants_feat16() const override { return true; }
 
     void forward(const NnSpan &sp, cudaStream_t s) override {
         const int total = sp.SC * sp.K;
         const int q_total = (total + tc::kTileM - 1) / tc::kTileM;
         const int QB = std::min(q_total, 2 * n_sm_);  // tiles per sub-batch
-        if (!sp.tiles_ready) a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
-        else tc::launch_tc_ctx_pack(sp.ctx, a0_.p, sp.SC, sp.K, s);
+        if (!sp.feat16) throw Error(FVAD_ERR_INVALID_ARGUMENT, "the tensor-core backend reads the fp16 feature rows");
+        a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
         x1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
         xp_.ensure((size_t)QB * kSteps * tc::tile_bytes(1200) / 2);
         h1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
@@ -220,10 +191,10 @@ public:
         f3_.ensure((size_t)QB * kFrames * tc::tile_bytes(608) / 2);
         for (int q0 = 0; q0 < q_total; q0 += QB) {
             const int Q = std::min(QB, q_total - q0);
-            const __half *a0 = sp.tiles_ready ? a0_.p + (size_t)q0 * kSteps * tc::tile_bytes(176) / 2 : a0_.p;
-            tc::PackArgs pa{sp.feat, a0_.p, Q, q0 * tc::kTileM, total, sp.K};
+            const __half *a0 = a0_.p;
+            tc::PackArgs pa{static_cast<const __half *>(sp.feat16), a0_.p, Q, q0 * tc::kTileM, total, sp.K};
             mark(0, s);
-            if (!sp.tiles_ready) tc::launch_tc_pack(pa, s);
+            tc::launch_tc_pack(pa, s);
             mark(1, s);
             gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
             mark(2, s);
@@ -306,8 +277,6 @@ private:
     bool gtraced_ = false;
     bool traced_ = false;
     bool pair_ = false;
-    bool fused_pack_ = false;  // FVAD_FUSED_PACK=1: the STFT writes the fp16 input tiles itself -- measured slower (its 16-byte
-                               // pieces land 2 KB apart and cost the STFT +75 %, more than the pack kernel's 5 ms), kept for A/B
     bool gemm_ts_ = true;     // A tile in TMEM (FVAD_GEMM_TS=0: resident in shared memory, the first design)
     bool gemm_pair_ = false;  // CTA-pair GEMM (FVAD_GEMM_PAIR=1): parity-green but 50 % slower than the one-CTA kernel, kept for A/B
 

@@ -64,14 +64,13 @@ void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
 // CTA-pair version (nn_tc_gru2.cu): Rimg is the split image (per chunk two 24-row halves tiled with R = 24)
 void launch_tc_gru2(const GruArgs &a, int n_sm, cudaStream_t s);
 
-// features f32 [SC][4+50K][161] -> fp16 tiles [q][54] of 176 columns for sequences seq0 .. seq0+128*Q-1
+// feature rows fp16 [SC][4+50K][176] -> fp16 tiles [q][54] of 176 columns for sequences seq0 .. seq0+128*Q-1
 struct PackArgs {
-    const float *feat;
+    const __half *feat16;
     __half *A0;
     int Q, seq0, n_seq, Kchunks;
 };
 void launch_tc_pack(const PackArgs &a, cudaStream_t s);
-void launch_tc_ctx_pack(const float *ctx, __half *A0, int SC, int K, cudaStream_t s);
 
 }  // namespace tc
 }  // namespace fvad

@@ -44,8 +44,8 @@ struct StftLaneConst {
 // frames f = warp, warp+10, ... of the tile xs -> spectrum rows / feature rows
 __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneConst &lc, const float *__restrict__ xs,
                                             float2 *__restrict__ Z, __half *__restrict__ fh, int sc, int c, int warp, int lane) {
-    // fh: this warp's 176-half staging row for the fused NN input pack (bins 161..175 stay zero)
-    if (a.nn_tiles && lane < 15) fh[kBins + lane] = __float2half(0.0f);
+    // fh: this warp's 176-half staging row for the fp16 feature rows (bins 161..175 stay zero)
+    if (a.feat16 && lane < 15) fh[kBins + lane] = __float2half(0.0f);
     for (int f = warp; f < kFrames; f += kStftWarps) {
         const float *fx = xs + f * kHop;
         float2 v[5];
@@ -61,20 +61,8 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
         const size_t row = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames + f;
         const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
         float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
-        float *frw = a.feat + frow * kBins;
-        // fused NN input pack: element (sequence g, step t, bin k) of the fp16 tiles, see nn_tc.cuh tiled_off
-        constexpr size_t kTileBytes = 128 * 176 * 2;
-        __half *t0 = nullptr, *t1 = nullptr;
-        if (a.nn_tiles) {
-            const int g = sc * a.K + c;
-            t0 = reinterpret_cast<__half *>(static_cast<uint8_t *>(a.nn_tiles) + ((size_t)(g >> 7) * kSteps + (f + kCtx)) * kTileBytes +
-                                            (size_t)((g & 127) >> 3) * 128 + (size_t)(g & 7) * 16);
-            if (f >= kFrames - kCtx && c + 1 < a.K) {
-                const int g1 = g + 1;
-                t1 = reinterpret_cast<__half *>(static_cast<uint8_t *>(a.nn_tiles) + ((size_t)(g1 >> 7) * kSteps + (f - (kFrames - kCtx))) * kTileBytes +
-                                                (size_t)((g1 & 127) >> 3) * 128 + (size_t)(g1 & 7) * 16);
-            }
-        }
+        float *frw = a.feat ? a.feat + frow * kBins : nullptr;
+        __half *h16 = a.feat16 ? static_cast<__half *>(a.feat16) + frow * 176 : nullptr;
         // real-FFT unpack in kissfft's pair form (kiss_fftr.c:93-116): the lane handles bins k and 160-k for
         // k = lane + 32q in [0, 80].  k = 0 runs through the same arithmetic with Z[0] as its own partner
         // (gives DC = x + y, Nyquist = x - y, imaginary parts 0, kiss_fftr.c:82-89); at k = 80 both stores hit
@@ -93,17 +81,14 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
                     // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate)
                     const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
                     const float ft = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
-                    frw[kk] = ft;
-                    if (t0) fh[kk] = __float2half_rn(ft);
+                    if (frw) frw[kk] = ft;
+                    if (h16) fh[kk] = __float2half_rn(ft);
                 }
             }
         }
         __syncwarp();
-        if (t0 && lane < 22) {  // 22 core columns of 8 bins: one 16-byte store each, 2 048 bytes apart
-            const uint4 v = *reinterpret_cast<const uint4 *>(fh + 8 * lane);
-            *reinterpret_cast<uint4 *>(reinterpret_cast<uint8_t *>(t0) + (size_t)lane * 2048) = v;
-            if (t1) *reinterpret_cast<uint4 *>(reinterpret_cast<uint8_t *>(t1) + (size_t)lane * 2048) = v;
-        }
+        if (h16 && lane < 22)  // the row leaves as 22 consecutive 16-byte stores
+            *reinterpret_cast<uint4 *>(h16 + 8 * lane) = *reinterpret_cast<const uint4 *>(fh + 8 * lane);
         __syncwarp();
     }
 }
