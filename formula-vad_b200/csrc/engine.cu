@@ -462,6 +462,7 @@ void Batch::push_any(const void *const *pcm, size_t n_pointers, size_t n, int me
     }
     if (fmt) pend_i16_.ensure((size_t)SC_ * chunk_);
 
+    if (pscan_.valid) issue_scan(nullptr);  // (only after a push that threw half-way)
     span_idx_ = 0;
     FVAD_CUDA_CHECK(cudaEventRecord(ev_[6], s));
     size_t src_off = 0;        // samples of the caller's buffers consumed by whole chunks
