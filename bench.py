@@ -30,9 +30,10 @@ FLOP_PER_FRAME_STEP = 2 * 2_681_000          # fc1 + 2 x (GRU W + GRU R) + fc2 +
 STEPS_PER_CHUNK, FRAMES_PER_CHUNK = 54, 50   # the reference evaluates 54 rows per 50 output frames
 
 
-def stft_bytes_per_frame(D: int, with_spec: bool) -> int:
-    # read 160*D new input samples, write 161 features (+ 161 complex bins when the spectrum is materialised)
-    return 160 * D * 4 + 161 * 4 + (161 * 8 if with_spec else 0)
+def stft_bytes_per_frame(D: int, with_spec: bool, fp16_rows: bool = False) -> int:
+    # read 160*D new input samples, write 161 features (f32, or a 176-half row for the tensor-core backend)
+    # (+ 161 complex bins when the spectrum is materialised)
+    return 160 * D * 4 + (176 * 2 if fp16_rows else 161 * 4) + (161 * 8 if with_spec else 0)
 
 
 def measured_peaks():
@@ -284,7 +285,7 @@ def run_native(args):
         nn_ms = stage[1] / args.steps
         stft_ms = stage[0] / args.steps
         ach_tf = nn_flop / (nn_ms * 1e-3) / 1e12 if nn_ms > 0 else 0.0
-        sb = frames * stft_bytes_per_frame(D, True)
+        sb = frames * stft_bytes_per_frame(D, True, args.nn_mode != "f32")
         ach_gbs = sb / (stft_ms * 1e-3) / 1e9 if stft_ms > 0 else 0.0
         # dominant kernel: one GRU layer launch (tc_gru_kernel; two layers, identical shapes).  Algorithmic flops of a
         # launch = its share of S*n_chunks sequences x 54 steps x 2*480000 (R.h of the layer).
@@ -308,7 +309,7 @@ def run_native(args):
                                 "traffic": None, "peak_source": f"{which} bf16_tflops_sustained"},
             "nn_layer_ms_per_step": {k: float(v) / args.steps for k, v in zip(names, layer_ms)},
             "stft_roofline": {"kernel": "stft_kernel", "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
-                              "frac": ach_gbs / hbm_peak, "traffic": None, "bytes_per_frame": stft_bytes_per_frame(D, True),
+                              "frac": ach_gbs / hbm_peak, "traffic": None, "bytes_per_frame": stft_bytes_per_frame(D, True, args.nn_mode != "f32"),
                               "peak_source": f"{which} hbm_gbs"},
             "e2e": {"value": world * audio_sec_per_step / (e2e_ms * 1e-3), "unit": "audio-sec/sec",
                     "h2d_bytes_per_step": int(S * n * 4), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
