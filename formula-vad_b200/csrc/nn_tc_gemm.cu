@@ -360,6 +360,10 @@ void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s) {
     if (pl.n_stages > kMaxStages) pl.n_stages = kMaxStages;
     pl.n_slabs = (a.K + pl.KS - 1) / pl.KS;
     if (pl.n_stages < 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: layer does not fit the shared-memory plan");
+    // With A in TMEM two consumers share the ring and each skips the other's stages, while a parity wait can only tell
+    // "this fill" from "the fill before".  The a_full / a_empty waits that precede every full-barrier wait guarantee the
+    // previous fill of the awaited stage is over exactly when the ring is at least as long as an A tile's slab count.
+    if (a.a_tmem && pl.n_stages < pl.n_slabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: ring shorter than the A tile's slabs");
     pl.bias_off = pl.a_bytes + pl.n_stages * pl.stage_bytes;
     pl.tr_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
     pl.sh_off = pl.tr_off + tr_bytes;
