@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(kIstftThreads) istft_kernel(IstftArgs a, const
     __shared__ float2 xb[kIstftWarps][kBins + 1];
 
     const int c = blockIdx.x, sc = blockIdx.y;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // (tells the compiler the warp index is uniform)
     for (int i = tid; i < 256; i += kIstftThreads) T[i] = gT[i];
     const float *__restrict__ wn = gwn;  // 1.25 KB, L1-resident; keeps static shared memory under 48 KB
     __syncthreads();

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(kStftThreads, 2) stft_kernel_d1(StftArgs a, co
     StftSmem1 &sm = *reinterpret_cast<StftSmem1 *>(smem_raw);
     const int sc = blockIdx.y;
     const int c_begin = blockIdx.x * kChunksPerCta, c_end = min(a.K, c_begin + kChunksPerCta);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // (tells the compiler the warp index is uniform)
     const float *__restrict__ xrow = a.x[sc] + a.x_offset;
 
     // chunk c -> buffer b: the 160 samples before the chunk are its halo (for the span's first chunk they come
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const fl
 
     const int c = blockIdx.x;    // chunk within the span
     const int sc = blockIdx.y;   // stream-channel
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // (tells the compiler the warp index is uniform)
 
     for (int i = tid; i < kNfft; i += kStftThreads) {
         if (i < 256) T[i] = gT[i];

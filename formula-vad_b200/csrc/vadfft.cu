@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(kVadThreads, D == 1 ? 2 : 1) vadfft_kernel(Vad
     __shared__ float2 zb[kVadWarps][512 + 32];  // one pad slot per 16: the bit-reversed store (stride 16) spreads over all banks
     __shared__ float2 hann2[512];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // (tells the compiler the warp index is uniform)
     for (int i = tid; i < 1024; i += kVadThreads) T[i] = gT[i];
     for (int i = tid; i < 512; i += kVadThreads) hann2[i] = reinterpret_cast<const float2 *>(ghann)[i];
     __syncthreads();
