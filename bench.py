@@ -45,6 +45,30 @@ def measured_peaks():
     return 6650.0, 1400.0, "fallback"  # B200_PROFILING.md fallback figures
 
 
+def ncu_traffic(kernel: str, streams: int, hours: float, sample_rate: int):
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one launch of `kernel`, from the committed
+    `ncu --set full` capture of this same workload (profiles/r01_traffic.json, written by tools/ncu_traffic.py);
+    None when no capture of this workload is on file."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        d = json.load(f)
+    w = d.get("workload", {})
+    if (w.get("streams"), w.get("hours"), w.get("sample_rate")) != (streams, hours, sample_rate):
+        return None
+    return d.get("kernels", {}).get(kernel, {}).get("dram_bytes_per_launch")
+
+
+def ncu_traffic_chunks(kernel: str):
+    """chunks per stream the captured launch covered (the first, full-size span of a step)"""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f).get("kernels", {}).get(kernel, {}).get("chunks_per_stream")
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -293,6 +317,9 @@ def run_native(args):
         gru_flop_total = 2.0 * args.steps * S * n_chunks * STEPS_PER_CHUNK * 2 * 480_000
         gru_tf = gru_flop_total / (gru_ms * 1e-3) / 1e12 if gru_ms > 0 else 0.0
         names = fv.capi.NN_LAYERS
+        kc = ncu_traffic_chunks("stft_kernel_d1")  # algorithmic bytes of the launch the ncu traffic figure belongs to
+        stft_traffic_alg = (S * kc * FRAMES_PER_CHUNK * stft_bytes_per_frame(D, True, args.nn_mode != "f32")
+                            if kc and ncu_traffic("stft_kernel_d1", S, args.hours, args.sample_rate) else None)
         out = {
             "metric": "realtime_factor_full_pipeline", "value": value, "unit": "audio-sec/sec", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "wall_ms_per_step": wall_ms / args.steps,
@@ -301,15 +328,17 @@ def run_native(args):
             "data": "synthetic", "config": workload_config(args),
             "stage_ms_per_step": {k: float(v) / args.steps for k, v in zip(["stft", "nsnet2", "istft", "vadfft", "vadscan"], stage)},
             "roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
-                         "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,
+                         "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,  # a stage of nine kernels; per-kernel traffic below
                          "peak_source": f"{which} bf16_tflops_sustained"},
             "kernel_roofline": {"kernel": "tc_gru_kernel (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
                                 "bound": "tensor", "achieved": gru_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": gru_tf / tf_peak,
                                 "avg_launch_ms": gru_ms / max(gru_n, 1), "flop_per_launch": gru_flop_total / max(gru_n, 1),
-                                "traffic": None, "peak_source": f"{which} bf16_tflops_sustained"},
+                                "traffic": ncu_traffic("tc_gru_kernel", S, args.hours, args.sample_rate),
+                                "peak_source": f"{which} bf16_tflops_sustained"},
             "nn_layer_ms_per_step": {k: float(v) / args.steps for k, v in zip(names, layer_ms)},
             "stft_roofline": {"kernel": "stft_kernel", "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
-                              "frac": ach_gbs / hbm_peak, "traffic": None, "bytes_per_frame": stft_bytes_per_frame(D, True, args.nn_mode != "f32"),
+                              "frac": ach_gbs / hbm_peak, "traffic": ncu_traffic("stft_kernel_d1", S, args.hours, args.sample_rate),
+                              "traffic_launch_algorithmic_bytes": stft_traffic_alg, "bytes_per_frame": stft_bytes_per_frame(D, True, args.nn_mode != "f32"),
                               "peak_source": f"{which} hbm_gbs"},
             "e2e": {"value": world * audio_sec_per_step / (e2e_ms * 1e-3), "unit": "audio-sec/sec",
                     "h2d_bytes_per_step": int(S * n * 4), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,

@@ -189,6 +189,16 @@ __device__ __forceinline__ void rfft_pair(float2 zk, float2 znk, float2 st, floa
     Xnk = make_float2((f1.x - t.x) * 0.5f, (t.y - f1.y) * 0.5f);
 }
 
+// rfft_pair for a transform whose input was pre-scaled by 1/2 (a kernel folds the 0.5 into its window: scaling
+// by a power of two commutes with every rounding, so the bins are bit-identical and four multiplies are saved).
+__device__ __forceinline__ void rfft_pair_halved(float2 zk, float2 znk, float2 st, float2 &Xk, float2 &Xnk) {
+    const float2 f1 = make_float2(zk.x + znk.x, zk.y - znk.y);
+    const float2 f2 = make_float2(zk.x - znk.x, zk.y + znk.y);
+    const float2 t = cmul(f2, st);
+    Xk = make_float2(f1.x + t.x, f1.y + t.y);
+    Xnk = make_float2(f1.x - t.x, t.y - f1.y);
+}
+
 // Inverse pre-pack (kiss_fftri, kiss_fftr.c:131-153): Zt[k] = (X[k]+conj(X[N-k])) + i*conj(T[k])*(X[k]-conj(X[N-k]))
 __device__ __forceinline__ float2 irfft_pack(const float2 *__restrict__ X, const float2 *__restrict__ T, int N, int k) {
     const float2 a = X[k];

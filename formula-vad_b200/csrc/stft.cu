@@ -32,7 +32,10 @@ struct StftLaneConst {
     __device__ __forceinline__ void init(const float2 *__restrict__ T, const float *__restrict__ win, int lane) {
         ftw.init(T, lane);
 #pragma unroll
-        for (int q = 0; q < 5; ++q) wreg[q] = *reinterpret_cast<const float2 *>(win + 2 * (lane + 32 * q));
+        for (int q = 0; q < 5; ++q) {  // window * 1/2: the real-FFT unpack's HALF_OF (kiss_fftr.c:111-114), applied up front
+            const float2 w = *reinterpret_cast<const float2 *>(win + 2 * (lane + 32 * q));
+            wreg[q] = make_float2(0.5f * w.x, 0.5f * w.y);
+        }
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
             const float2 t = T[(lane + 32 * q) & 255];  // pairs k = lane + 32q <= 80 are used
@@ -40,6 +43,12 @@ struct StftLaneConst {
         }
     }
 };
+
+__device__ __forceinline__ float lg2_ftz(float x) {
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 
 // frames f = warp, warp+10, ... of the tile xs -> spectrum rows / feature rows
 __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneConst &lc, const float *__restrict__ xs,
@@ -52,7 +61,7 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
 #pragma unroll
         for (int q = 0; q < 5; ++q) {
             const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * (lane + 32 * q));
-            v[q] = make_float2(s2.x * lc.wreg[q].x, s2.y * lc.wreg[q].y);  // FFT.zig:188-196 window multiply
+            v[q] = make_float2(s2.x * lc.wreg[q].x, s2.y * lc.wreg[q].y);  // FFT.zig:188-196 window multiply (and the 1/2)
         }
         warp_cfft_tw<5, false>(v, lc.ftw);
 #pragma unroll
@@ -72,15 +81,16 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
             const int k = lane + 32 * q;
             if (q < 2 || k <= kHop / 2) {
                 float2 X[2];
-                rfft_pair(Z[k], Z[k ? kHop - k : 0], lc.st[q], X[0], X[1]);
+                rfft_pair_halved(Z[k], Z[k ? kHop - k : 0], lc.st[q], X[0], X[1]);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int kk = h ? kHop - k : k;
                     if (srow) srow[kk] = X[h];
                     // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no
-                    // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate)
+                    // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate).  The
+                    // operand is >= 1e-12, never subnormal, so the .ftz form (one MUFU, no rescale sequence) is exact here.
                     const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
-                    const float ft = __log2f(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
+                    const float ft = lg2_ftz(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
                     if (frw) frw[kk] = ft;
                     if (h16) fh[kk] = __float2half_rn(ft);
                 }
