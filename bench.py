@@ -28,6 +28,7 @@ import numpy as np  # noqa: E402
 # algorithmic work per unit.  Unit = one NSNet2 frame hop (10 ms of one channel).
 FLOP_PER_FRAME_STEP = 2 * 2_681_000          # fc1 + 2 x (GRU W + GRU R) + fc2 + fc3 + fc4, MAC x 2
 STEPS_PER_CHUNK, FRAMES_PER_CHUNK = 54, 50   # the reference evaluates 54 rows per 50 output frames
+ISTFT_BYTES_PER_FRAME = 161 * 8 + 161 * 4 + 160 * 4  # spectrum row + f32 gain row read, one hop of y16 written
 
 
 def stft_bytes_per_frame(D: int, with_spec: bool, fp16_rows: bool = False) -> int:
@@ -70,7 +71,9 @@ def ncu_traffic_chunks(kernel: str):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe).  The sampler is started
+    before the warm-up steps (nvidia-smi needs a second or more to come up on an 8-GPU box, longer than a short timed
+    region) and every line is stamped when it is read; stop(t0, t1) keeps the lines that fall inside the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -89,9 +92,9 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.perf_counter(), ln.strip()))
 
-    def stop(self) -> dict:
+    def stop(self, t_begin: float = 0.0, t_end: float = float("inf")) -> dict:
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -101,7 +104,11 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for ts, ln in self.lines if t_begin <= ts <= t_end + 0.03]
+        window = "timed region"
+        if not inside:  # sampling slower than the region: the warm-up steps are the same workload at the same load
+            inside, window = [ln for _, ln in self.lines], "warm-up + timed region"
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -118,7 +125,8 @@ class ClockSampler:
         thr = 0.5 * max(pw)
         load = [s for s, p in zip(sm, pw) if p >= thr] or sm
         return {"sm_mhz": float(np.median(load)), "sm_mhz_min": float(min(load)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
-                "power_w_median": float(np.median([p for p in pw if p >= thr] or pw)), "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_median": float(np.median([p for p in pw if p >= thr] or pw)), "samples": len(sm), "window": window,
+                "reasons": sorted(reasons)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -153,6 +161,61 @@ def cpu_pipeline_throughput(fv, wd, sample_rate: int, n_threads: int, seconds_ea
     return audio, times, nseg
 
 
+_JSON_FD = None
+_ORIG_AFFINITY = None
+
+
+def protect_stdout():
+    """The contract is ONE JSON line on stdout; libraries (NCCL prints its version banner there) must not add to it:
+    everything else that writes to fd 1 goes to stderr, the JSON line goes to the original stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(out: dict):
+    line = (json.dumps(out) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
+
+def bind_to_gpu_numa(local: int):
+    """Pin this rank to the CPUs next to its GPU (sysfs local_cpulist of the GPU's PCI function) before any pinned
+    host memory is allocated, so first-touch places the staging buffers on the GPU's own NUMA node.  Returns the cpulist
+    used, or None when it cannot be determined (the run continues unpinned)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local)).busId
+        if isinstance(bus, bytes):
+            bus = bus.decode()
+        bus = bus.lower()
+        if bus.count(":") == 2 and len(bus.split(":")[0]) == 8:
+            bus = bus[4:]  # nvml prints an 8-digit domain, sysfs a 4-digit one
+        with open(f"/sys/bus/pci/devices/{bus}/local_cpulist") as f:
+            cpulist = f.read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        global _ORIG_AFFINITY
+        _ORIG_AFFINITY = os.sched_getaffinity(0)
+        cpus &= _ORIG_AFFINITY
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpulist
+    except Exception:  # noqa: BLE001 -- best effort; an unpinned run is still a valid run
+        return None
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -177,7 +240,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def workload_config(args):
@@ -200,6 +263,7 @@ def run_native(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    host_cpus = bind_to_gpu_numa(local) if not os.environ.get("FVAD_NO_NUMA_BIND") else None
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -239,11 +303,11 @@ def run_native(args):
     clocks = ClockSampler(local)
 
     # ---- device-resident arm ----
+    clocks.start()
     for _ in range(args.warmup):
         gp.push_pointers(dev_ptrs, n, on_device=True)
     st0 = gp.stats()
     barrier()
-    clocks.start()
     t0 = time.perf_counter()
     dev_ms = 0.0
     stage = np.zeros(5)
@@ -256,8 +320,9 @@ def run_native(args):
         layer_ms += st["last_nn_layer_ms"]
         layer_n += st["last_nn_layer_launches"]
     barrier()
-    wall_ms = 1e3 * (time.perf_counter() - t0)
-    clk = clocks.stop()
+    t1 = time.perf_counter()
+    wall_ms = 1e3 * (t1 - t0)
+    clk = clocks.stop(t0, t1)
     st1 = gp.stats()
     launches = st1["kernel_launches"] - st0["kernel_launches"]
     n_segments = sum(len(gp.segments(s)) for s in range(S))
@@ -308,6 +373,7 @@ def run_native(args):
         nn_flop = S * n_chunks * STEPS_PER_CHUNK * FLOP_PER_FRAME_STEP
         nn_ms = stage[1] / args.steps
         stft_ms = stage[0] / args.steps
+        istft_ms = stage[2] / args.steps  # the stage also holds two small carry copies (kilobytes)
         ach_tf = nn_flop / (nn_ms * 1e-3) / 1e12 if nn_ms > 0 else 0.0
         sb = frames * stft_bytes_per_frame(D, True, args.nn_mode != "f32")
         ach_gbs = sb / (stft_ms * 1e-3) / 1e9 if stft_ms > 0 else 0.0
@@ -340,6 +406,14 @@ def run_native(args):
                               "frac": ach_gbs / hbm_peak, "traffic": ncu_traffic("stft_kernel_d1", S, args.hours, args.sample_rate),
                               "traffic_launch_algorithmic_bytes": stft_traffic_alg, "bytes_per_frame": stft_bytes_per_frame(D, True, args.nn_mode != "f32"),
                               "peak_source": f"{which} hbm_gbs"},
+            "istft_roofline": {"kernel": "istft_stream_kernel", "bound": "hbm",
+                               "achieved": frames * ISTFT_BYTES_PER_FRAME / (istft_ms * 1e-3) / 1e9 if istft_ms > 0 else 0.0,
+                               "peak": hbm_peak, "unit": "GB/s",
+                               "frac": (frames * ISTFT_BYTES_PER_FRAME / (istft_ms * 1e-3) / 1e9 / hbm_peak) if istft_ms > 0 else 0.0,
+                               "traffic": ncu_traffic("istft_stream_kernel", S, args.hours, args.sample_rate),
+                               "traffic_launch_algorithmic_bytes": (S * kc * FRAMES_PER_CHUNK * ISTFT_BYTES_PER_FRAME
+                                                                    if kc and ncu_traffic("istft_stream_kernel", S, args.hours, args.sample_rate) else None),
+                               "bytes_per_frame": ISTFT_BYTES_PER_FRAME, "peak_source": f"{which} hbm_gbs"},
             "e2e": {"value": world * audio_sec_per_step / (e2e_ms * 1e-3), "unit": "audio-sec/sec",
                     "h2d_bytes_per_step": int(S * n * 4), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
                     "steps": e2e_steps, "input": "pinned host f32 planar (the reference's pushSamples type), double-buffered H2D"},
@@ -347,15 +421,18 @@ def run_native(args):
                         "h2d_bytes_per_step": int(S * n * 2), "ms_per_step": e2e16_ms, "steps": e2e_steps,
                         "input": "pinned host int16 PCM, converted on the device"},
             "gpu_launches": int(launches), "segments_found": int(n_segments), "clocks": clk,
+            "host_affinity": host_cpus,
         }
         # CPU baseline on a bounded sample (N=1 only)
         if world == 1 and not args.no_cpu_baseline:
+            if _ORIG_AFFINITY:
+                os.sched_setaffinity(0, _ORIG_AFFINITY)  # the CPU arm uses every host core
             cores = os.cpu_count() or 1
             audio, times, _ = cpu_pipeline_throughput(fv, wd, sr, cores, args.cpu_seconds)
             out["cpu_baseline"] = {"value": audio / times[0], "unit": "audio-sec/sec", "cores": cores, "kind": "port",
                                    "sample": f"{cores} streams x {args.cpu_seconds:.0f} s, one thread per stream (oracle port of the "
                                              f"reference pipeline; reference binary unavailable: no zig/onnxruntime on this box)"}
-        print(json.dumps(out), flush=True)
+        emit(out)
     gp.close()
     if world > 1:
         dist.barrier()
@@ -379,6 +456,7 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "native":
         print("bench.py: warning: W < 3 warm-up steps breaks the timing rules", file=sys.stderr)
+    protect_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -120,9 +120,13 @@ __global__ void __launch_bounds__(kIstftThreads) istft_chunk_kernel(IstftArgs a,
 // ---- streaming warps ----
 constexpr int kIsWarps = 8;
 constexpr int kIsThreads = 32 * kIsWarps;
-constexpr int kIsCtasPerSm = 3;
+// CTAs per SM (A/B with FVAD_ISTFT_CTAS, ms per 20 stream-hours on one box): 2 -> 117 registers, 5.17; 3 -> 80 registers,
+// 5.89; 4 -> 64 registers with 132 B of spills, 7.5.  With room for the 18 prefetch registers the next frame's loads
+// issue a whole transform ahead; more resident warps do not make up for losing that.
+constexpr int kIsCtasPerSm = 2;
 
-__global__ void __launch_bounds__(kIsThreads, kIsCtasPerSm) istft_stream_kernel(IstftArgs a, const float2 *__restrict__ gT,
+template <int CTAS>
+__global__ void __launch_bounds__(kIsThreads, CTAS) istft_stream_kernel(IstftArgs a, const float2 *__restrict__ gT,
                                                                                 const float *__restrict__ gwn, int L,
                                                                                 int runs_per_sc, int total_runs) {
     __shared__ float2 T[256];
@@ -232,10 +236,10 @@ __global__ void __launch_bounds__(kIsThreads, kIsCtasPerSm) istft_stream_kernel(
 }
 
 // run length: the one in [24, 64] that wastes least on the partial last wave and on the 1/L redundant frame
-static int pick_run_length(int rows, int SC) {
+static int pick_run_length(int rows, int SC, int ctas) {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-    const double slots = (double)sms * kIsCtasPerSm * kIsWarps;
+    const double slots = (double)sms * ctas * kIsWarps;
     int best = 40;
     double best_cost = 1e30;
     for (int L = 24; L <= 64; ++L) {
@@ -253,10 +257,14 @@ void launch_istft(const IstftArgs &a, const Tables &t, cudaStream_t s) {
     if (!chunk_variant) {
         const int rows = kFrames * a.K;
         static int cached_rows = -1, cached_sc = -1, cached_L = 0;
-        if (rows != cached_rows || a.SC != cached_sc) cached_L = pick_run_length(rows, a.SC), cached_rows = rows, cached_sc = a.SC;
+        static const int ctas = getenv("FVAD_ISTFT_CTAS") ? atoi(getenv("FVAD_ISTFT_CTAS")) : kIsCtasPerSm;
+        if (rows != cached_rows || a.SC != cached_sc) cached_L = pick_run_length(rows, a.SC, ctas), cached_rows = rows, cached_sc = a.SC;
         const int L = cached_L;
         const int runs_per_sc = (rows + L - 1) / L, total = runs_per_sc * a.SC;
-        istft_stream_kernel<<<(unsigned)((total + kIsWarps - 1) / kIsWarps), kIsThreads, 0, s>>>(a, t.T320, t.win320n, L, runs_per_sc, total);
+        const unsigned grid = (unsigned)((total + kIsWarps - 1) / kIsWarps);
+        if (ctas == 4) istft_stream_kernel<4><<<grid, kIsThreads, 0, s>>>(a, t.T320, t.win320n, L, runs_per_sc, total);
+        else if (ctas == 3) istft_stream_kernel<3><<<grid, kIsThreads, 0, s>>>(a, t.T320, t.win320n, L, runs_per_sc, total);
+        else istft_stream_kernel<kIsCtasPerSm><<<grid, kIsThreads, 0, s>>>(a, t.T320, t.win320n, L, runs_per_sc, total);
         FVAD_LAUNCHED();
         FVAD_CUDA_CHECK(cudaGetLastError());
         return;

@@ -11,7 +11,7 @@ scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 tscale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0}
 out = {}
 for r in rows[2:]:
-    name = r[ki].split("(")[0].split("::")[-1].split("<")[0].strip()
+    name = r[ki].split("(")[0].split("::")[-1].split("<")[0].replace("void ", "").strip()
     if name in out:
         continue
     rd = float(r[ri].replace(",", "")) * scale[units[ri]]
