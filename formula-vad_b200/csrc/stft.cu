@@ -124,7 +124,7 @@ struct StftSmem1 {
     float2 T[256];
     float win[kNfft];
     float2 zb[kStftWarps][kHop];
-    float red[kStftWarps];
+    float red[2][kStftWarps];
     __align__(16) __half fh[kStftWarps][176];
     uint64_t full[2];
 };
@@ -164,8 +164,6 @@ __global__ void __launch_bounds__(kStftThreads, 2) stft_kernel_d1(StftArgs a, co
 
     for (int c = c_begin, it = 0; c < c_end; ++c, ++it) {
         const int b = it & 1;
-        // the other buffer was last read in the previous iteration, which ended with __syncthreads
-        if (tid == 0 && c + 1 < c_end) prefetch(c + 1, b ^ 1);
         tc::mbar_wait(&sm.full[b], (it >> 1) & 1);
         float *xs = sm.xs[b];
         if (c == 0 && tid < kHop) xs[tid] = a.halo_in[(size_t)sc * kHop + tid];
@@ -178,10 +176,14 @@ __global__ void __launch_bounds__(kStftThreads, 2) stft_kernel_d1(StftArgs a, co
             ss = fmaf(v.z, v.z, ss);
             ss = fmaf(v.w, v.w, ss);
         }
-        stft_sumsq(a, ss, sm.red, sc, c, tid);  // contains a __syncthreads: the halo rows are visible after it
+        // The reduction's __syncthreads is the only block barrier of a chunk: every warp that passes it has finished the
+        // frames of chunk c-1, so the other buffer is free and the prefetch of chunk c+1 goes out right behind it (a
+        // whole chunk of transforms ahead of its use); it also makes the halo rows visible.  The partial sums alternate
+        // between two rows so the next chunk's writes are a barrier away from this chunk's reads.
+        stft_sumsq(a, ss, sm.red[b], sc, c, tid);
+        if (tid == 0 && c + 1 < c_end) prefetch(c + 1, b ^ 1);
         if (c == a.K - 1 && tid < kHop) a.halo_out[(size_t)sc * kHop + tid] = xs[kFrames * kHop + tid];
         stft_frames(a, lc, xs, sm.zb[warp], sm.fh[warp], sc, c, warp, lane);
-        __syncthreads();
     }
 }
 
