@@ -359,11 +359,27 @@ def run_native(args):
     e2e16_ms = 1e3 * (time.perf_counter() - t0) / e2e_steps
     gp2.close()
 
+    # ---- the link the e2e arm is bound by: plain pinned-host -> device copies of the same buffer, all ranks at once ----
+    link_bytes = min(xq.numel() * 2, 2 << 30)
+    src = xq.view(-1)[:link_bytes // 2]
+    dst = torch.empty(link_bytes // 2, dtype=torch.int16, device=f"cuda:{local}")
+    dst.copy_(src, non_blocking=True)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(3):
+        dst.copy_(src, non_blocking=True)
+    ev1.record()
+    barrier()
+    link_gbs = 3 * link_bytes / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    del dst, src, xq
+
     # max over ranks
-    tt = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e16_ms], dtype=torch.float64, device=f"cuda:{local}")
+    tt = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e16_ms, -link_gbs], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    dev_ms, wall_ms, e2e_ms, e2e16_ms = [float(v) for v in tt.tolist()]
+    dev_ms, wall_ms, e2e_ms, e2e16_ms, link_gbs = [float(v) for v in tt.tolist()]
+    link_gbs = -link_gbs  # the slowest rank's link
 
     if rank == 0:
         hbm_peak, tf_peak, which = measured_peaks()
@@ -416,7 +432,11 @@ def run_native(args):
                                "bytes_per_frame": ISTFT_BYTES_PER_FRAME, "peak_source": f"{which} hbm_gbs"},
             "e2e": {"value": world * audio_sec_per_step / (e2e_ms * 1e-3), "unit": "audio-sec/sec",
                     "h2d_bytes_per_step": int(S * n * 4), "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms,
-                    "steps": e2e_steps, "input": "pinned host f32 planar (the reference's pushSamples type), double-buffered H2D"},
+                    "steps": e2e_steps, "input": "pinned host f32 planar (the reference's pushSamples type), double-buffered H2D",
+                    "h2d_link_gbs": link_gbs, "h2d_achieved_gbs": S * n * 4 / (e2e_ms * 1e-3) / 1e9,
+                    "h2d_frac_of_link": (S * n * 4 / (e2e_ms * 1e-3) / 1e9) / link_gbs if link_gbs > 0 else None,
+                    "link_note": "h2d_link_gbs = plain pinned-host -> device copies of 2 GiB on every rank at once "
+                                 "(slowest rank); the f32 arm is bound by it"},
             "e2e_i16": {"value": world * audio_sec_per_step / (e2e16_ms * 1e-3), "unit": "audio-sec/sec",
                         "h2d_bytes_per_step": int(S * n * 2), "ms_per_step": e2e16_ms, "steps": e2e_steps,
                         "input": "pinned host int16 PCM, converted on the device"},
