@@ -409,10 +409,10 @@ def run_native(args):
             "dtype": {"f32": "f32", "f16x3": "f16x3-split (fp32 accumulate)", "f16": "f16 (fp32 accumulate)"}[args.nn_mode],
             "data": "synthetic", "config": workload_config(args),
             "stage_ms_per_step": {k: float(v) / args.steps for k, v in zip(["stft", "nsnet2", "istft", "vadfft", "vadscan"], stage)},
-            "roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
+            "nn_stage_roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
                          "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,  # a stage of nine kernels; per-kernel traffic below
                          "peak_source": f"{which} bf16_tflops_sustained"},
-            "kernel_roofline": {"kernel": "tc_gru_kernel (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
+            "roofline": {"kernel": "tc_gru_kernel (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
                                 "bound": "tensor", "achieved": gru_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": gru_tf / tf_peak,
                                 "avg_launch_ms": gru_ms / max(gru_n, 1), "flop_per_launch": gru_flop_total / max(gru_n, 1),
                                 "traffic": ncu_traffic("tc_gru_kernel", S, args.hours, args.sample_rate),
