@@ -237,8 +237,9 @@ __global__ void __launch_bounds__(kIsThreads, CTAS) istft_stream_kernel(IstftArg
 
 // run length: the one in [24, 64] that wastes least on the partial last wave and on the 1/L redundant frame
 static int pick_run_length(int rows, int SC, int ctas) {
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const double slots = (double)sms * ctas * kIsWarps;
     int best = 40;
     double best_cost = 1e30;
@@ -256,7 +257,7 @@ void launch_istft(const IstftArgs &a, const Tables &t, cudaStream_t s) {
     static const bool chunk_variant = getenv("FVAD_ISTFT_CHUNK") != nullptr;
     if (!chunk_variant) {
         const int rows = kFrames * a.K;
-        static int cached_rows = -1, cached_sc = -1, cached_L = 0;
+        thread_local int cached_rows = -1, cached_sc = -1, cached_L = 0;  // (any L is correct; the cache only saves the search)
         static const int ctas = getenv("FVAD_ISTFT_CTAS") ? atoi(getenv("FVAD_ISTFT_CTAS")) : kIsCtasPerSm;
         if (rows != cached_rows || a.SC != cached_sc) cached_L = pick_run_length(rows, a.SC, ctas), cached_rows = rows, cached_sc = a.SC;
         const int L = cached_L;

@@ -14,6 +14,8 @@
 // the other half of a double-buffered tile with cp.async.bulk + mbarrier while the warps transform
 // the current one, so no warp ever waits on HBM; at D = 3 the decimating loads are batched.
 // Algorithmic HBM bytes per frame: 160*D*4 read + 161*4 features (+ 161*8 spectrum) written.
+#include <cstdlib>
+
 #include "fft_dev.cuh"
 #include "kernels.cuh"
 #include "tc_dev.cuh"
@@ -50,6 +52,48 @@ __device__ __forceinline__ float lg2_ftz(float x) {
     return r;
 }
 
+// one windowed frame v (lane l holds samples 2(l+32q), 2(l+32q)+1) -> its spectrum row / feature rows
+__device__ __forceinline__ void stft_emit(const StftArgs &a, const StftLaneConst &lc, float2 (&v)[5], float2 *__restrict__ Z,
+                                          __half *__restrict__ fh, int sc, int c, int f, int lane) {
+    warp_cfft_tw<5, false>(v, lc.ftw);
+#pragma unroll
+    for (int k1 = 0; k1 < 5; ++k1) Z[cfft_out_index<5>(lane, k1)] = v[k1];
+    __syncwarp();
+    const size_t row = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames + f;
+    const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
+    float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
+    float *frw = a.feat ? a.feat + frow * kBins : nullptr;
+    __half *h16 = a.feat16 ? static_cast<__half *>(a.feat16) + frow * 176 : nullptr;
+    // real-FFT unpack in kissfft's pair form (kiss_fftr.c:93-116): the lane handles bins k and 160-k for
+    // k = lane + 32q in [0, 80].  k = 0 runs through the same arithmetic with Z[0] as its own partner
+    // (gives DC = x + y, Nyquist = x - y, imaginary parts 0, kiss_fftr.c:82-89); at k = 80 both stores hit
+    // bin 80 and the second wins, as in kissfft.
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const int k = lane + 32 * q;
+        if (q < 2 || k <= kHop / 2) {
+            float2 X[2];
+            rfft_pair_halved(Z[k], Z[k ? kHop - k : 0], lc.st[q], X[0], X[1]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int kk = h ? kHop - k : k;
+                if (srow) srow[kk] = X[h];
+                // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no
+                // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate).  The
+                // operand is >= 1e-12, never subnormal, so the .ftz form (one MUFU, no rescale sequence) is exact here.
+                const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
+                const float ft = lg2_ftz(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
+                if (frw) frw[kk] = ft;
+                if (h16) fh[kk] = __float2half_rn(ft);
+            }
+        }
+    }
+    __syncwarp();
+    if (h16 && lane < 22)  // the row leaves as 22 consecutive 16-byte stores
+        *reinterpret_cast<uint4 *>(h16 + 8 * lane) = *reinterpret_cast<const uint4 *>(fh + 8 * lane);
+    __syncwarp();
+}
+
 // frames f = warp, warp+10, ... of the tile xs -> spectrum rows / feature rows
 __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneConst &lc, const float *__restrict__ xs,
                                             float2 *__restrict__ Z, __half *__restrict__ fh, int sc, int c, int warp, int lane) {
@@ -63,43 +107,7 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
             const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * (lane + 32 * q));
             v[q] = make_float2(s2.x * lc.wreg[q].x, s2.y * lc.wreg[q].y);  // FFT.zig:188-196 window multiply (and the 1/2)
         }
-        warp_cfft_tw<5, false>(v, lc.ftw);
-#pragma unroll
-        for (int k1 = 0; k1 < 5; ++k1) Z[cfft_out_index<5>(lane, k1)] = v[k1];
-        __syncwarp();
-        const size_t row = (size_t)sc * (kFrames * a.K) + (size_t)c * kFrames + f;
-        const size_t frow = (size_t)sc * (kCtx + kFrames * a.K) + kCtx + (size_t)c * kFrames + f;
-        float2 *srow = a.spec ? reinterpret_cast<float2 *>(a.spec) + row * kBins : nullptr;
-        float *frw = a.feat ? a.feat + frow * kBins : nullptr;
-        __half *h16 = a.feat16 ? static_cast<__half *>(a.feat16) + frow * 176 : nullptr;
-        // real-FFT unpack in kissfft's pair form (kiss_fftr.c:93-116): the lane handles bins k and 160-k for
-        // k = lane + 32q in [0, 80].  k = 0 runs through the same arithmetic with Z[0] as its own partner
-        // (gives DC = x + y, Nyquist = x - y, imaginary parts 0, kiss_fftr.c:82-89); at k = 80 both stores hit
-        // bin 80 and the second wins, as in kissfft.
-#pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            const int k = lane + 32 * q;
-            if (q < 2 || k <= kHop / 2) {
-                float2 X[2];
-                rfft_pair_halved(Z[k], Z[k ? kHop - k : 0], lc.st[q], X[0], X[1]);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int kk = h ? kHop - k : k;
-                    if (srow) srow[kk] = X[h];
-                    // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no
-                    // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate).  The
-                    // operand is >= 1e-12, never subnormal, so the .ftz form (one MUFU, no rescale sequence) is exact here.
-                    const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
-                    const float ft = lg2_ftz(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
-                    if (frw) frw[kk] = ft;
-                    if (h16) fh[kk] = __float2half_rn(ft);
-                }
-            }
-        }
-        __syncwarp();
-        if (h16 && lane < 22)  // the row leaves as 22 consecutive 16-byte stores
-            *reinterpret_cast<uint4 *>(h16 + 8 * lane) = *reinterpret_cast<const uint4 *>(fh + 8 * lane);
-        __syncwarp();
+        stft_emit(a, lc, v, Z, fh, sc, c, f, lane);
     }
 }
 
@@ -187,6 +195,79 @@ __global__ void __launch_bounds__(kStftThreads, 2) stft_kernel_d1(StftArgs a, co
     }
 }
 
+// ---- D = 1, A/B option FVAD_STFT_STREAM=1: independent streaming warps (the ISTFT's structure) ----
+// A warp owns one chunk: it reads each frame's 320 samples straight from global memory (the half shared with the
+// previous frame hits L1), with the next frame's loads in flight while this one is transformed; the chunk's sum of
+// squares accumulates over each frame's new hop.  No tile, no block barrier.
+constexpr int kSsWarps = 8;
+constexpr int kSsThreads = 32 * kSsWarps;
+
+struct StftSmemS {
+    float2 T[256];
+    float win[kNfft];
+    float2 zb[kSsWarps][kHop];
+    __align__(16) __half fh[kSsWarps][176];
+};
+
+__global__ void __launch_bounds__(kSsThreads, 2) stft_stream_kernel(StftArgs a, const float2 *__restrict__ gT,
+                                                                    const float *__restrict__ gwin) {
+    __shared__ StftSmemS sm;
+    const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    for (int i = tid; i < kNfft; i += kSsThreads) {
+        if (i < 256) sm.T[i] = gT[i];
+        sm.win[i] = gwin[i];
+    }
+    __syncthreads();
+    const int item = blockIdx.x * kSsWarps + warp;
+    if (item >= a.K * a.SC) return;
+    const int sc = item / a.K, c = item - sc * a.K;
+    StftLaneConst lc;
+    lc.init(sm.T, sm.win, lane);
+    float2 *Z = sm.zb[warp];
+    __half *fh = sm.fh[warp];
+    if (a.feat16 && lane < 15) fh[kBins + lane] = __float2half(0.0f);
+
+    // frame f of the chunk = samples [160 (f-1), 160 (f-1) + 320) relative to the chunk start
+    const float *__restrict__ xc = a.x[sc] + a.x_offset + (size_t)c * kChunk16;
+    const float *__restrict__ halo = a.halo_in + (size_t)sc * kHop;
+    float2 nx[5];
+    auto fetch = [&](int f) {
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            const int j = lane + 32 * q;  // float2 index inside the frame; j < 80 is the hop shared with frame f-1
+            const float *src = (c == 0 && f == 0 && j < kHop / 2) ? halo + 2 * j : xc + (f - 1) * kHop + 2 * j;
+            nx[q] = __ldg(reinterpret_cast<const float2 *>(src));
+        }
+    };
+    fetch(0);
+    float ss = 0.0f;
+    for (int f = 0; f < kFrames; ++f) {
+        float2 v[5], raw[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) raw[q] = nx[q];
+        if (f + 1 < kFrames) fetch(f + 1);
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            if (lane + 32 * q >= kHop / 2) {  // the frame's new hop: this chunk's own samples
+                ss = fmaf(raw[q].x, raw[q].x, ss);
+                ss = fmaf(raw[q].y, raw[q].y, ss);
+            }
+            v[q] = make_float2(raw[q].x * lc.wreg[q].x, raw[q].y * lc.wreg[q].y);
+        }
+        if (f == kFrames - 1 && c == a.K - 1) {  // the span's last hop is the next span's halo
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+                const int j = lane + 32 * q;
+                if (j >= kHop / 2) reinterpret_cast<float2 *>(a.halo_out + (size_t)sc * kHop)[j - kHop / 2] = raw[q];
+            }
+        }
+        stft_emit(a, lc, v, Z, fh, sc, c, f, lane);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (lane == 0) a.sumsq[(size_t)sc * (a.K + 1) + 1 + c] = ss;
+}
+
 // ---- general D (48 kHz input: D = 3): one chunk per CTA, decimating loads ----
 struct StftSmemD {
     float xs[kXs];
@@ -262,7 +343,11 @@ __global__ void __launch_bounds__(kStftThreads) stft_kernel(StftArgs a, const fl
 
 void launch_stft(const StftArgs &a, const Tables &t, cudaStream_t s) {
     if (a.K <= 0 || a.SC <= 0) return;
-    if (a.D == 1) {
+    static const bool stream_variant = getenv("FVAD_STFT_STREAM") != nullptr;
+    if (a.D == 1 && stream_variant) {
+        const int items = a.K * a.SC;
+        stft_stream_kernel<<<(unsigned)((items + kSsWarps - 1) / kSsWarps), kSsThreads, 0, s>>>(a, t.T320, t.win320);
+    } else if (a.D == 1) {
         static bool attr = false;
         if (!attr) {
             FVAD_CUDA_CHECK(cudaFuncSetAttribute(stft_kernel_d1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StftSmem1)));
