@@ -18,8 +18,24 @@
 
 namespace fvad {
 
+// Packed FP32 pairs (sm_100: FADD2 / FFMA2, one issue slot for both components of a complex value).  The spectral
+// kernels are issue-bound, so complex add / subtract / scale-and-add go through these; each component is the same
+// IEEE operation as the scalar form (a - b as fma(b, -1, a) is exact in the product), so results do not change.
+// The complex multiply stays scalar: its packed form needs a swapped copy of an operand, which costs the slots back.
+#ifndef FVAD_F32X2
+#define FVAD_F32X2 1
+#endif
+#if FVAD_F32X2
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a); }
+__device__ __forceinline__ float2 cfma(float2 a, float2 s, float2 c) { return __ffma2_rn(a, s, c); }
+__device__ __forceinline__ float2 cscale(float2 a, float2 s) { return __fmul2_rn(a, s); }
+#else
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cfma(float2 a, float2 s, float2 c) { return make_float2(fmaf(a.x, s.x, c.x), fmaf(a.y, s.y, c.y)); }
+__device__ __forceinline__ float2 cscale(float2 a, float2 s) { return make_float2(a.x * s.x, a.y * s.y); }
+#endif
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
     return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
@@ -82,15 +98,16 @@ struct RegDft<5, INV> {
         constexpr float s1 = 0.95105651629515357f, s2 = 0.58778525229247313f;   // sin(2pi/5), sin(4pi/5)
         const float2 a1 = cadd(v[1], v[4]), d1 = csub(v[1], v[4]);
         const float2 a2 = cadd(v[2], v[3]), d2 = csub(v[2], v[3]);
-        const float2 A = make_float2(v[0].x + c1 * a1.x + c2 * a2.x, v[0].y + c1 * a1.y + c2 * a2.y);
-        const float2 B = make_float2(v[0].x + c2 * a1.x + c1 * a2.x, v[0].y + c2 * a1.y + c1 * a2.y);
+        const float2 C1 = make_float2(c1, c1), C2 = make_float2(c2, c2), S1 = make_float2(s1, s1), S2 = make_float2(s2, s2);
+        const float2 A = cfma(a2, C2, cfma(a1, C1, v[0]));
+        const float2 B = cfma(a2, C1, cfma(a1, C2, v[0]));
         // P = s1*d1 + s2*d2 ; Q = s2*d1 - s1*d2 ; forward: Y1 = A - iP, Y4 = A + iP, Y2 = B - iQ, Y3 = B + iQ
-        const float2 P = make_float2(s1 * d1.x + s2 * d2.x, s1 * d1.y + s2 * d2.y);
-        const float2 Q = make_float2(s2 * d1.x - s1 * d2.x, s2 * d1.y - s1 * d2.y);
+        const float2 P = cfma(d2, S2, cscale(d1, S1));
+        const float2 Q = cfma(d2, make_float2(-s1, -s1), cscale(d1, S2));
         // -i*(x+iy) = (y, -x)
         const float2 mP = INV ? make_float2(-P.y, P.x) : make_float2(P.y, -P.x);
         const float2 mQ = INV ? make_float2(-Q.y, Q.x) : make_float2(Q.y, -Q.x);
-        v[0] = make_float2(v[0].x + a1.x + a2.x, v[0].y + a1.y + a2.y);
+        v[0] = cadd(cadd(v[0], a1), a2);
         v[1] = cadd(A, mP);
         v[4] = csub(A, mP);
         v[2] = cadd(B, mQ);
@@ -152,9 +169,10 @@ __device__ __forceinline__ void warp_cfft_tw(float2 (&v)[R], const WarpFftTw<R, 
         const int h = 16 >> i;
 #pragma unroll
         for (int k1 = 0; k1 < R; ++k1) {
-            float2 a;
-            a.x = fmaf(v[k1].x, w.sg[i], __shfl_xor_sync(0xffffffffu, v[k1].x, h));
-            a.y = fmaf(v[k1].y, w.sg[i], __shfl_xor_sync(0xffffffffu, v[k1].y, h));
+            float2 b;
+            b.x = __shfl_xor_sync(0xffffffffu, v[k1].x, h);
+            b.y = __shfl_xor_sync(0xffffffffu, v[k1].y, h);
+            const float2 a = cfma(v[k1], make_float2(w.sg[i], w.sg[i]), b);
             v[k1] = i < 4 ? cmul(a, w.ws[i]) : a;  // the last stage's twiddle is 1 for every lane
         }
     }
@@ -192,10 +210,10 @@ __device__ __forceinline__ void rfft_pair(float2 zk, float2 znk, float2 st, floa
 // rfft_pair for a transform whose input was pre-scaled by 1/2 (a kernel folds the 0.5 into its window: scaling
 // by a power of two commutes with every rounding, so the bins are bit-identical and four multiplies are saved).
 __device__ __forceinline__ void rfft_pair_halved(float2 zk, float2 znk, float2 st, float2 &Xk, float2 &Xnk) {
-    const float2 f1 = make_float2(zk.x + znk.x, zk.y - znk.y);
-    const float2 f2 = make_float2(zk.x - znk.x, zk.y + znk.y);
+    const float2 f1 = cfma(znk, make_float2(1.0f, -1.0f), zk);  // (zk.x + znk.x, zk.y - znk.y), exact products
+    const float2 f2 = cfma(znk, make_float2(-1.0f, 1.0f), zk);  // (zk.x - znk.x, zk.y + znk.y)
     const float2 t = cmul(f2, st);
-    Xk = make_float2(f1.x + t.x, f1.y + t.y);
+    Xk = cadd(f1, t);
     Xnk = make_float2(f1.x - t.x, t.y - f1.y);
 }
 

@@ -201,17 +201,17 @@ __global__ void __launch_bounds__(kIsThreads, CTAS) istft_stream_kernel(IstftArg
         for (int q = 0; q < 5; ++q) {  // kiss_fftri pre-pack (kiss_fftr.c:131-153)
             const int k = lane + 32 * q;
             const float2 xa = X[k], xb2 = X[kHop - k];
-            const float2 e = make_float2(xa.x + xb2.x, xa.y - xb2.y), d = make_float2(xa.x - xb2.x, xa.y + xb2.y);
+            const float2 e = cfma(xb2, make_float2(1.0f, -1.0f), xa), d = cfma(xb2, make_float2(-1.0f, 1.0f), xa);  // exact products
             v[q] = cadd(e, cmul(d, itw[q]));
         }
         warp_cfft_tw<5, true>(v, ftw);
 #pragma unroll
         for (int k1 = 0; k1 < 5; ++k1)  // NSNet2.zig:335-336: inv *= window*norm
-            v[k1] = make_float2(__fmul_rn(v[k1].x, wreg[k1].x), __fmul_rn(v[k1].y, wreg[k1].y));
+            v[k1] = cscale(v[k1], wreg[k1]);  // (a packed multiply rounds each component: nothing to contract with)
         if (g >= g0 && even) {
 #pragma unroll
             for (int k1 = 0; k1 < 5; ++k1)  // out += inv: this frame's head + the previous frame's tail
-                reinterpret_cast<float2 *>(hb)[nb + k1] = make_float2(__fadd_rn(v[k1].x, carry[k1].x), __fadd_rn(v[k1].y, carry[k1].y));
+                reinterpret_cast<float2 *>(hb)[nb + k1] = cadd(v[k1], carry[k1]);
         }
 #pragma unroll
         for (int k1 = 0; k1 < 5; ++k1) {

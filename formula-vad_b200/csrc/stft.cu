@@ -81,7 +81,8 @@ __device__ __forceinline__ void stft_emit(const StftArgs &a, const StftLaneConst
                 // NSNet2.zig:275-284: log10(max(re^2 + im^2, 1e-12)), squares and sum rounded separately (no
                 // FMA); the logarithm is the hardware lg2 (abs error ~1e-7 in log10 units, inside every gate).  The
                 // operand is >= 1e-12, never subnormal, so the .ftz form (one MUFU, no rescale sequence) is exact here.
-                const float pw = __fadd_rn(__fmul_rn(X[h].x, X[h].x), __fmul_rn(X[h].y, X[h].y));
+                const float2 sq = cscale(X[h], X[h]);  // both squares in one packed multiply, each rounded on its own
+                const float pw = __fadd_rn(sq.x, sq.y);
                 const float ft = lg2_ftz(fmaxf(pw, 1e-12f)) * 0.30102999566398120f;
                 if (frw) frw[kk] = ft;
                 if (h16) fh[kk] = __float2half_rn(ft);
@@ -105,7 +106,7 @@ __device__ __forceinline__ void stft_frames(const StftArgs &a, const StftLaneCon
 #pragma unroll
         for (int q = 0; q < 5; ++q) {
             const float2 s2 = *reinterpret_cast<const float2 *>(fx + 2 * (lane + 32 * q));
-            v[q] = make_float2(s2.x * lc.wreg[q].x, s2.y * lc.wreg[q].y);  // FFT.zig:188-196 window multiply (and the 1/2)
+            v[q] = cscale(s2, lc.wreg[q]);  // FFT.zig:188-196 window multiply (and the 1/2)
         }
         stft_emit(a, lc, v, Z, fh, sc, c, f, lane);
     }
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(kSsThreads, 2) stft_stream_kernel(StftArgs a, 
                 ss = fmaf(raw[q].x, raw[q].x, ss);
                 ss = fmaf(raw[q].y, raw[q].y, ss);
             }
-            v[q] = make_float2(raw[q].x * lc.wreg[q].x, raw[q].y * lc.wreg[q].y);
+            v[q] = cscale(raw[q], lc.wreg[q]);
         }
         if (f == kFrames - 1 && c == a.K - 1) {  // the span's last hop is the next span's halo
 #pragma unroll
