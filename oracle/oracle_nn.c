@@ -8,7 +8,7 @@
  *   z = s(Wz x + Rz h + Wbz + Rbz);  r = s(Wr x + Rr h + Wbr + Rbr)
  *   n = tanh(Wh x + Wbh + r * (Rh h + Rbh));  h' = (1-z)*n + z*h
  * Third-party arithmetic being restated: onnxruntime 1.15.0 CPU EP (prebuilt, absent from the
- * snapshot) -- PARITY UNPINNED; cross-checked against torch.nn.GRU in tests/test_oracle_nn.py.
+ * snapshot) -- PARITY UNPINNED; cross-checked against torch.nn.GRU in tests/test_oracle_cpu.py.
  */
 #include "fvad_oracle.h"
 
