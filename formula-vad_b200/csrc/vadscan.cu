@@ -7,14 +7,21 @@
 //   VADPipeline.stateMachineStep alt loop (src/AudioPipeline/VADPipeline.zig:231-236): M machines
 //   with different Configs over the same frame results (BASELINE config 5).
 //
-// The reference recomputes each rolling mean as sum_i data[i]*(1/n) on every push (O(window));
-// here each ring keeps an f64 running sum (add the new value, subtract the evicted one).  The ring
-// values are f32 numbers widened to f64, so the running sum is exact whenever the window's dynamic
-// range is below 2^29 and otherwise differs from the reference's own rounding by ~1e-13 relative.
+// The reference recomputes each rolling mean as sum_i data[i]*(1/n) on every push (O(window)).
+// Here the short-term and ratio means are evaluated exactly so (fast path); the long-term ring
+// (8 437 slots) keeps an f64 running sum -- add the new value, subtract the evicted one -- that is
+// RE-DERIVED from the ring every time the write index wraps (once per n_long pushes, ~3 min of
+// audio), so rounding never accumulates beyond one turn of the ring.  The ring values are f32
+// numbers widened to f64: the running sum is exact while the window's dynamic range stays below
+// 2^29 / n_long (then it equals the reference's sum up to the reference's own per-term rounding)
+// and otherwise carries at most one window's worth of f64 rounding.
 //
-// One thread per (stream, machine): the scan is a true recurrence (the long-term mean is frozen
-// while the threshold is met), 46.875 steps per stream-second.  Latency-bound by construction;
-// the engine overlaps it with the next span's network on another CUDA stream.
+// Two kernels: `vadscan_warp_kernel` (the engine's path) runs one WARP per (stream, machine) and
+// advances the long-term recurrence by runs of frames; `vadscan_kernel` (window sizes outside the
+// fast path's limits) runs one thread per (stream, machine), frame by frame.  The scan is a true
+// recurrence (the long-term mean is frozen while the threshold is met), 46.875 steps per
+// stream-second: latency-bound by construction; the engine overlaps it with the next span's
+// network on another CUDA stream.
 #include "kernels.cuh"
 
 namespace fvad {
@@ -123,6 +130,12 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_kernel(ScanArgs a) {
             if (!met) {
                 st.last_avg = ring_push(ring_long, mc.n_long, st.long_idx, st.long_cnt, st.long_sum, min_volume);
                 st.has_last = 1;
+                if (st.long_idx == 0) {  // the ring has turned over once: re-derive the running sum from its contents
+                    double acc = 0.0;
+                    for (int k = 0; k < mc.n_long; ++k) acc += ring_long[k];
+                    st.long_sum = acc;
+                    st.last_avg = acc * (1.0 / (double)st.long_cnt);
+                }
             }
             if (met_out) met_out[i] = met ? 1 : 0;
             fsm_step(st, mc, met, meta_ratio, index, segs, a.max_segments);
@@ -228,6 +241,7 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
             const bool vrok = valid && (s_vr[j] > mc.ratio_threshold);
             unsigned metmask = 0;
             int cur = 0;
+            int wrapped = 0;  // the long ring's write index passed slot 0 in this block
             if (L.has_last && L.cnt == mc.n_long) {
                 for (int it = 0; it < kMaxIters && cur < nl; ++it) {
                     // ---- no frame from the cursor on meets the threshold: every one of them is pushed ----
@@ -256,7 +270,7 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
                         L.sum += shfl_d(inc, f - 1);
                         L.last_avg = L.sum * L.inv;
                         L.idx += np;
-                        if (L.idx >= mc.n_long) L.idx -= mc.n_long;
+                        if (L.idx >= mc.n_long) { L.idx -= mc.n_long; wrapped = 1; }
                         L.k += np;
                     }
                     cur = f;
@@ -284,6 +298,7 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
                             L.sum = (L.sum - old) + nv;
                             ring_long[L.idx] = nv;
                             L.idx = (L.idx + 1 == mc.n_long) ? 0 : L.idx + 1;
+                            if (L.idx == 0) wrapped = 1;
                             if (L.cnt < mc.n_long) {
                                 ++L.cnt;
                                 L.inv = 1.0 / (double)L.cnt;
@@ -300,6 +315,20 @@ __global__ void __launch_bounds__(kScanThreads) vadscan_warp_kernel(ScanArgs a) 
                 L.idx = __shfl_sync(0xffffffffu, L.idx, 0); L.cnt = __shfl_sync(0xffffffffu, L.cnt, 0);
                 L.has_last = __shfl_sync(0xffffffffu, L.has_last, 0); L.k = __shfl_sync(0xffffffffu, L.k, 0);
                 metmask = __shfl_sync(0xffffffffu, metmask, 0);
+                wrapped = __shfl_sync(0xffffffffu, wrapped, 0);
+            }
+            if (wrapped) {
+                // One turn of the ring since the last re-derivation: replace the running sum (n_long add/subtract
+                // pairs of rounding) by the sum of what the ring holds now -- what the reference sums on every push
+                // (RollingAverage.zig:45-56).  All values are >= 0, so the lane-strided tree sum is within a few ulp
+                // of the array-order sum; ~3 us per 3 minutes of audio.
+                __syncwarp();  // this block's ring stores (other lanes) are visible
+                double part = 0.0;
+                for (int k = lane; k < mc.n_long; k += 32) part += ring_long[k];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                L.sum = part;
+                if (L.has_last) L.last_avg = L.sum * L.inv;
             }
             if (met_out && valid) met_out[i0 + j] = (unsigned char)((metmask >> lane) & 1u);
             // ---- state machine + statistics: sequential, but idle while closed with nothing met ----

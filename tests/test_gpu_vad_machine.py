@@ -103,3 +103,31 @@ def test_segment_overflow_is_counted_not_written(fv):
     vm = fv.VADMachine(fv.vad_machine_config(min_vad_duration_sec=0.0, max_speech_gap_sec=0.1), SR, FFT, max_segments=2)
     met, segs = vm.scan(band[None, :], ratio)
     assert len(segs[0]) == 2
+
+
+@pytest.mark.parametrize("over,step", [
+    (dict(), 0),                                     # warp kernel (run-based long-term recurrence), one launch
+    (dict(), 37888),                                 # ... state carried across launches the size of an engine span
+    (dict(long_term_speech_avg_sec=9.0), 0),         # n_long = 421 < 514: the one-thread-per-machine kernel
+])
+def test_multi_hour_loud_then_silent_series(fv, po, over, step):
+    """Three hours whose first minutes are 10^7 times louder than the rest: while loud values share the long-term
+    window with quiet ones the f64 running sum loses the quiet values' low bits, and once the loud ones are evicted a
+    never-resynchronised sum would keep that error for the rest of the stream (the reference re-sums the ring on every
+    push, RollingAverage.zig:45-56).  vadscan.cu re-derives the sum from the ring once per turn; the decisions must stay
+    identical to the oracle's over the whole series."""
+    n = int(3 * 3600 * SR / FFT)
+    rng = np.random.default_rng(2024)
+    band = (2e-7 * np.exp(0.4 * rng.standard_normal(n))).astype(np.float32)
+    band[:30000] *= np.float32(1e7)                   # ~10 minutes around 2.0
+    ratio = np.full(n, 0.9, np.float32)
+    f = 35000
+    while f < n - 2000:                                # speech bursts 8-60x over the quiet floor, also near the threshold
+        ln = int(rng.integers(30, 400))
+        band[f:f + ln] *= np.float32(rng.uniform(8, 60))
+        f += ln + int(rng.integers(200, 3000))
+    g_met, g_segs = fv.VADMachine(fv.vad_machine_config(**over), SR, FFT).scan(band[None, :], ratio, frames_per_launch=step)
+    o_met, o_segs = _oracle_scan(po, po.VadMachineConfig.default(**over), band, ratio)
+    assert 1000 < o_met.sum() < n - 1000
+    assert np.array_equal(g_met[0], o_met), int((g_met[0] != o_met).sum())
+    assert [(a, b) for a, b, _, _ in g_segs[0]] == [(a, b) for a, b, _, _ in o_segs] and len(o_segs) > 10
