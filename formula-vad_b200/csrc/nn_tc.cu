@@ -59,6 +59,7 @@ struct Layer {  // one dense layer prepared for launch_tc_gemm
     DevBuf<float> bias;
     int K = 0, Nc = 0, n_valid = 0, n_tiles = 0;
     int a_tmem = 0;  // GemmArgs::a_tmem for this layer (the N-tiles were cut for it)
+    tc::PairMaps maps;  // CTA-pair kernel: tensor maps over img2 (built when the layer runs on pairs)
     int nt_size[tc::kMaxNTiles] = {}, nt_col[tc::kMaxNTiles] = {};
     unsigned nt_off[tc::kMaxNTiles] = {};
 };
@@ -66,7 +67,7 @@ struct Layer {  // one dense layer prepared for launch_tc_gemm
 // Build the fp16 image of W [N][Kin] (row-major f32) with rows taken in the order perm[] (size
 // n_valid; nullptr = identity), padded to the N-tiles `tiles` and to Kp columns.
 void build_layer(Layer &L, const float *W, const float *bias, const int *perm, int n_valid, int Kin, int Kp,
-                 const std::vector<int> &tiles) {
+                 const std::vector<int> &tiles, bool pair = false) {
     L.K = Kp; L.n_valid = n_valid; L.n_tiles = (int)tiles.size();
     int col = 0; size_t off = 0;
     for (size_t j = 0; j < tiles.size(); ++j) {
@@ -108,6 +109,8 @@ void build_layer(Layer &L, const float *W, const float *bias, const int *perm, i
     FVAD_CUDA_CHECK(cudaMemcpy(L.img2.p, img2.data(), img2.size() * sizeof(__half), cudaMemcpyHostToDevice));
     L.bias.ensure(b.size());
     FVAD_CUDA_CHECK(cudaMemcpy(L.bias.p, b.data(), b.size() * sizeof(float), cudaMemcpyHostToDevice));
+    memset(&L.maps, 0, sizeof(L.maps));
+    if (pair) tc::build_pair_maps(L.maps, L.img2.p, Kp, L.n_tiles, L.nt_size, L.nt_off);
 }
 
 class NnTc final : public NnBackend {
@@ -134,13 +137,14 @@ public:
         for (int c = 0; c < 25; ++c)
             for (int g = 0; g < 3; ++g)
                 for (int u = 0; u < 16; ++u) perm[(size_t)(48 * c + 16 * g + u)] = g * H + 16 * c + u;
-        build_layer(fc1_, w.fc1_w.data(), w.fc1_b.data(), nullptr, H, 161, 176, {208, 192});
+        const bool gp = gemm_pair_;
+        build_layer(fc1_, w.fc1_w.data(), w.fc1_b.data(), nullptr, H, 161, 176, {208, 192}, gp);
         for (int l = 0; l < 2; ++l) {
             // xp bias: Wb + Rb for z and r; Wb alone for n (Rb_n is applied inside r*(.), nn_tc_gru.cu)
             std::vector<float> b(3 * H);
             for (int i = 0; i < 3 * H; ++i) b[(size_t)i] = w.gru_Wb[l][(size_t)i] + (i < 2 * H ? w.gru_Rb[l][(size_t)i] : 0.0f);
             build_layer(gW_[l], w.gru_W[l].data(), b.data(), perm.data(), 3 * H, H, H,
-                        ts ? T{144, 144, 144, 144, 144, 144, 144, 144, 48} : T{240, 240, 240, 240, 240});
+                        (ts || gp) ? T{144, 144, 144, 144, 144, 144, 144, 144, 48} : T{240, 240, 240, 240, 240}, gp);
             // R: 25 chunk images of 48 rows = one "layer" with 25 N-tiles of 48
             Layer tmp;
             std::vector<__half> img((size_t)3 * H * H);
@@ -165,9 +169,10 @@ public:
             gRbn_[l].ensure((size_t)H);
             FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
         }
-        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, T{208, 208, 192});
-        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, T{208, 208, 192});
-        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, ts ? T{96, 80} : T{176});
+        // CTA pairs keep every layer's A tile in TMEM (K/2 columns): N-tiles of at most (512 - K/2)/2 columns, multiples of 16
+        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, gp ? T{128, 128, 128, 112, 112} : T{208, 208, 192}, gp);
+        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, gp ? T{96, 96, 96, 96, 96, 96, 32} : T{208, 208, 192}, gp);
+        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, (ts || gp) ? T{96, 80} : T{176}, gp);
         // A in TMEM caps the N-tile at (512 - K/2)/2 columns: 144 at K = 400, 96 at K = 608.  Measured per 20 stream-hours:
         // fc1 2.12 -> 1.75 ms, W1/W2 8.6 -> 7.5, fc4 3.43 -> 3.2; fc2 unchanged (4.0) and fc3 (K = 608, N-tile 96) 7.3 -> 8.8,
         // so those two keep A in shared memory with N-tiles of 208
@@ -198,21 +203,6 @@ public:
             mark(1, s);
             gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
             mark(2, s);
-            if (const char *tp = getenv("FVAD_GEMM_TRACE")) {
-                if (!gtraced_) {  // debug only: CTA 0's timeline of the first W1 launch
-                    gtraced_ = true;
-                    const size_t ne = 5 * 4 * 8 * 32;
-                    gtrace_.ensure(ne);
-                    FVAD_CUDA_CHECK(cudaMemsetAsync(gtrace_.p, 0, ne * 8, s));
-                    GemmArgs g = base_args(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0);
-                    g.trace = gtrace_.p;
-                    tc::launch_tc_gemm(g, n_sm_, s);
-                    std::vector<unsigned long long> h(ne);
-                    FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
-                    FVAD_CUDA_CHECK(cudaMemcpy(h.data(), gtrace_.p, ne * 8, cudaMemcpyDeviceToHost));
-                    if (FILE *f = fopen(tp, "wb")) { fwrite(h.data(), 8, ne, f); fclose(f); }
-                }
-            }
             gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             mark(3, s);
             gru(0, h1_.p, Q, 0, s);
@@ -228,7 +218,7 @@ public:
             mark(8, s);
             GemmArgs g = base_args(fc4_, f3_.p, nullptr, Q, kFrames, kFrames, 0, kFrames, 0, 2);
             g.out_mode = 1; g.gains = sp.gains; g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
-            launch(g, s);
+            launch(g, fc4_, s);
             mark(9, s);
             ++batches_;
         }
@@ -308,12 +298,34 @@ private:
         g.mt_count = Q * T; g.T = T; g.A_q = A_q; g.A_t0 = A_t0; g.C_q = C_q; g.C_t0 = C_t0; g.act = act;
         return g;
     }
-    void launch(const GemmArgs &g, cudaStream_t s) {
-        if (gemm_pair_) tc::launch_tc_gemm2(g, n_sm_, s);
+    void launch(const GemmArgs &g, const Layer &L, cudaStream_t s) {
+        if (gemm_pair_) tc::launch_tc_gemm2(g, L.maps, n_sm_, s);
         else tc::launch_tc_gemm(g, n_sm_, s);
     }
     void gemm(const Layer &L, const __half *A, __half *C, int Q, int T, int A_q, int A_t0, int C_q, int C_t0, int act, cudaStream_t s) {
-        launch(base_args(L, A, C, Q, T, A_q, A_t0, C_q, C_t0, act), s);
+        GemmArgs g = base_args(L, A, C, Q, T, A_q, A_t0, C_q, C_t0, act);
+        maybe_trace(g, L, s);
+        launch(g, L, s);
+    }
+    // debug only (FVAD_GEMM_TRACE=<file> [FVAD_GEMM_TRACE_LAYER=fc1|W1|W2|fc2|fc3]): one extra launch of that layer with
+    // CTA 0's timeline probe on, dumped to the file (tools/gemm_trace.py, tools/gemm_pair_trace.py)
+    void maybe_trace(GemmArgs g, const Layer &L, cudaStream_t s) {
+        const char *tp = getenv("FVAD_GEMM_TRACE");
+        if (!tp || gtraced_) return;
+        const char *want = getenv("FVAD_GEMM_TRACE_LAYER");
+        const Layer *sel = &gW_[0];
+        if (want) sel = !strcmp(want, "fc1") ? &fc1_ : !strcmp(want, "W2") ? &gW_[1] : !strcmp(want, "fc2") ? &fc2_ : !strcmp(want, "fc3") ? &fc3_ : &gW_[0];
+        if (sel != &L) return;
+        gtraced_ = true;
+        const size_t ne = 5 * 4 * 8 * 32;
+        gtrace_.ensure(ne);
+        FVAD_CUDA_CHECK(cudaMemsetAsync(gtrace_.p, 0, ne * 8, s));
+        g.trace = gtrace_.p;
+        launch(g, L, s);
+        std::vector<unsigned long long> h(ne);
+        FVAD_CUDA_CHECK(cudaStreamSynchronize(s));
+        FVAD_CUDA_CHECK(cudaMemcpy(h.data(), gtrace_.p, ne * 8, cudaMemcpyDeviceToHost));
+        if (FILE *f = fopen(tp, "wb")) { fwrite(h.data(), 8, ne, f); fclose(f); }
     }
 };
 

@@ -2,6 +2,7 @@
 #pragma once
 #include "common.cuh"
 
+#include <cuda.h>
 #include <cuda_fp16.h>
 
 namespace fvad {
@@ -43,8 +44,15 @@ struct GemmArgs {
     int seq0, n_seq, Kchunks;  // scatter: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
 };
 void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s);
-// CTA-pair version (nn_tc_gemm2.cu), reads a.B2
-void launch_tc_gemm2(const GemmArgs &a, int n_sm, cudaStream_t s);
+
+// CTA-pair version (nn_tc_gemm2.cu; cta_group::2, M = 256, A in TMEM).  The weights come from the pair image B2 through
+// TMA: one tensor map per (N-tile, half), passed to the kernel as a __grid_constant__ parameter.
+struct PairMaps {
+    CUtensorMap m[2 * kMaxNTiles];
+};
+int pair_slab_ksteps(int K);
+void build_pair_maps(PairMaps &maps, const void *img2, int K, int n_tiles, const int *nt_size, const unsigned *nt_off);
+void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStream_t s);
 
 // One GRU layer over 54 steps for Q tiles of 128 sequences.
 //   xp:   tiles [q][54] of 1200 columns: W x_t + Wb (+Rb for z,r), columns in chunk-interleaved order

@@ -1,15 +1,42 @@
-// nn_tc_gemm2.cu -- the dense-layer GEMM of nn_tc_gemm.cu on CTA PAIRS (tcgen05 cta_group::2, M = 256).
+// nn_tc_gemm2.cu -- the dense-layer GEMM of nn_tc_gemm.cu on CTA PAIRS (tcgen05 cta_group::2, M = 256), with the
+// weight halves delivered by TMA straight onto the MMA leader's barrier.
 //
-// Why pairs: the one-CTA kernel keeps its 128-row A tile (102 KB at K = 400) resident and streams the weight
-// matrix through what is left of shared memory.  Its timeline (tools/gemm_trace.py, profiles/r01_gemm_timeline.txt)
-// shows the ring is bytes-in-flight bound: a 30 KB stage lands 1 400-2 400 cycles after it is requested, three
-// stages fit, the tensor pipe wants one every 480 cycles and gets one every ~830.  In a pair each CTA stores only
-// HALF of every weight stage (N/2 rows) -- the tensor cores of both SMs read both halves -- so the same ring holds
-// twice the look-ahead, the L2 stream per SM halves and so does the shared-memory write+read traffic.
+// Replaces the MatMul/Add/Relu/Sigmoid nodes that onnxruntime executes inside `onnx_instance.run()` (reference
+// src/NSNet2.zig:220) -- fc1, the GRU input projections W x + b for all 54 steps at once, fc2, fc3, fc4 -- like
+// nn_tc_gemm.cu, whose math, operand layouts and epilogue it shares.
 //
-// Same math, roles and epilogue as nn_tc_gemm.cu.  Differences: cluster (2,1,1); CTA rank r owns M-tile 2*pair + r;
-// only rank 0 issues MMAs and commits (multicast to both CTAs' barriers); a relay thread in the peer forwards its
-// `full` / `a_full` completions to the leader; the peer's epilogue releases accumulators on the leader's barrier.
+// Why pairs.  A one-CTA M = 128 tile needs 2 bytes of weights per 2*128 flop: 64 B/clk/SM at the full tensor rate,
+// next to ~27 B/clk/SM of activation reads and writes, against an L2 that delivers ~43 B/clk/SM with all SMs pulling
+// (B300_MICROARCH: ~6 300 B/clk chip-wide, path-independent; measured here as 58 B/clk at the power-capped SM
+// clock, profiles/r01_gemm_timeline_a_in_tmem.txt).  The one-CTA kernel is therefore L2-bound at ~2/3 of the tensor
+// rate whatever its pipeline depth.  In a pair each CTA stores HALF of every weight stage (N/2 rows) and the tensor
+// cores of both SMs read both halves, so the weight stream per SM halves.
+//
+// What makes it fast (the first pair kernel, with a relay thread forwarding the peer's barrier completions and
+// cluster-scope barrier operations, was 50 % slower than one CTA):
+//   * each CTA's half of a weight stage is a TMA tile load (cp.async.bulk.tensor, .cta_group::2) whose bytes complete
+//     on the LEADER's `full` barrier -- the MMA issuer waits on one local barrier for both halves, no relay;
+//   * every barrier arrive and wait, the remote ones too, uses the default CTA-scope semantics (tc_dev.cuh:
+//     mbar_arrive_addr): `.acquire.cluster` polls stalled the issuer until its own MMAs had retired and
+//     `.release.cluster` arrives made the epilogue drain its global stores before handing an accumulator back;
+//   * the A tile (this CTA's own 128 rows) lives in TENSOR MEMORY (K/2 columns, A-from-TMEM MMAs): its K slabs come
+//     through their own staging buffers with their own producer thread, so they never occupy weight stages (in the
+//     one-CTA kernel the next tile's A slabs sit in the ring until the previous tile's MMAs free the TMEM columns,
+//     which stalls the weight prefetch for a whole L2 latency at every M-tile change);
+//   * two MMA-issuing threads, one per accumulator (even / odd N-tiles): one's barrier round trips, descriptor
+//     arithmetic and commits hide under the other's issue burst (an N = 96 slab of 8 MMAs is 384 tensor cycles,
+//     a lone issuer needs ~450 per slab);
+//   * the epilogue loads the accumulator one 32-column chunk ahead of its arithmetic and hands the accumulator
+//     back as soon as its last chunk sits in registers.
+//
+// Roles (both CTAs run all of them except the MMA issuers): warp 0 weight producer (TMA), warp 3 A producer
+// (cp.async.bulk), warps 1 and 2 MMA issuers (leader only; commits multicast to both CTAs; warp 2 also owns the TMEM
+// allocation), warps 4..7 epilogue (own 128 rows), warps 8..11 A stagers (staging buffer -> TMEM, tcgen05.st), and
+// for the gains output (NSETS = 2: its scatter is store-latency bound) warps 12..15 as a second epilogue set on
+// alternate 32-column chunks.  The f16 layers stay at 384 threads x <= 128 registers so the VAD scan's one-warp CTAs
+// can still share the SM (a GEMM CTA that owns the whole register file cannot start next to them).
+#include <cuda.h>
+
 #include "nn_tc.cuh"
 #include "tc_dev.cuh"
 
@@ -18,89 +45,99 @@ namespace tc {
 
 namespace {
 
-constexpr int kMaxSlabs = 40;
-constexpr int kMaxStages = 8;
-constexpr int kGemmThreads = 256;
+constexpr int kMaxSlabs = 8;
+constexpr int kMaxStages = 16;
+constexpr int kMaxABuf = 5;
 constexpr int kSmemTotal = 214 * 1024;  // see nn_tc_gemm.cu: leaves room for the concurrently running VAD scan
-#define GEMM_TRACE(kind, im, j, sl) do { } while (0)
 
-struct GemmShared {
-    uint64_t full[kMaxStages], peer_full[kMaxStages], empty[kMaxStages];
-    uint64_t a_full[kMaxSlabs], peer_a_full[kMaxSlabs], a_empty[kMaxSlabs], acc_full[2], acc_empty[2];
+// timeline probe (CTA 0 = the leader of pair 0, first 4 M-pairs, first 8 N-tiles): [kind][mpair][ntile][slot], kinds:
+// 0 weight producer issued slab, 1 MMA full ok, 2 MMA slab issued+committed, 3 epilogue acc_full ok (slot 0) / done (slot 1)
+// and MMA a_full[sl] ok (slot 2+sl, N-tile 0), 4 MMA acc_empty ok (slot 0) / accumulator committed (slot 1) and the
+// stagers' a_empty ok / as_full ok / staged / stored (slot 2+sl of N-tiles 0 / 1 / 2 / 3)
+#define PAIR_TRACE(kind, im, j, sl) do { if (a.trace && blockIdx.x == 0 && (im) < 4 && (j) < 8) \
+    a.trace[(((kind) * 4 + (im)) * 8 + (j)) * 32 + (sl)] = (unsigned long long)clock64(); } while (0)
+
+struct PairShared {
+    uint64_t full[kMaxStages];    // LEADER's copy is the live one: both CTAs' weight halves complete their bytes here
+    uint64_t empty[kMaxStages];   // per CTA: the leader's MMAs over this stage are done (multicast commit)
+    uint64_t as_full[kMaxABuf];   // per CTA: an A slab has landed in staging buffer i
+    uint64_t as_empty[kMaxABuf];  // per CTA: the stagers have moved it to TMEM
+    uint64_t a_full[kMaxSlabs];   // LEADER's: A slab sl is in TMEM in BOTH CTAs (2 arrivals)
+    uint64_t a_empty[kMaxSlabs];  // per CTA: the MMAs of the M-pair's last two N-tiles (one per issuer) over TMEM slab sl are done
+    uint64_t acc_full[2];         // per CTA: accumulator complete (multicast commit)
+    uint64_t acc_empty[2];        // LEADER's: drained by the epilogue warps of both CTAs (8 * NSETS arrivals)
     uint32_t tmem_base;
 };
 
-struct GemmPlan {  // host-computed shared-memory plan (stage_bytes is per CTA: half of a weight stage)
-    int KS, n_slabs, n_stages, stage_bytes, a_bytes, bias_off, tr_off, sh_off, smem_bytes;
+struct PairPlan {  // host-computed (launch_tc_gemm2)
+    int ks;             // K-steps of 16 columns per slab
+    int nk_total;       // K / 16
+    int n_slabs, n_stages, n_abuf;
+    int stage_bytes;    // per CTA: max over N-tiles of (NT/2 rows) x (ks K-steps) fp16
+    int a_slab_bytes;   // 128 rows x ks K-steps fp16
+    int b_off, bias_off, tr_off, sh_off, smem_bytes;
+    int acc_cols;       // TMEM columns between the two accumulators (max NT); A starts at 2*acc_cols
 };
 
-template <int ACT, int OUT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) tc_gemm2_kernel(const GemmArgs a, const GemmPlan pl) {
+template <int ACT, int OUT, int NSETS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS - 1), 1)
+    tc_gemm_pair_kernel(const GemmArgs a, const PairPlan pl, const __grid_constant__ PairMaps maps) {
+    constexpr int kThreads = 384 + 128 * (NSETS - 1);
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t *sA = smem, *sB = smem + pl.a_bytes;
+    uint8_t *sAst = smem, *sB = smem + pl.b_off;
     float *bias_s = reinterpret_cast<float *>(smem + pl.bias_off);
-    GemmShared *sh = reinterpret_cast<GemmShared *>(smem + pl.sh_off);
+    PairShared *sh = reinterpret_cast<PairShared *>(smem + pl.sh_off);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
     const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
     const int n_mpairs = (a.mt_count + 1) >> 1;
+    const int ks = pl.ks, n_slabs = pl.n_slabs, n_stages = pl.n_stages, n_abuf = pl.n_abuf;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < pl.n_stages; ++i) {
+        for (int i = 0; i < n_stages; ++i) {
             mbar_init(&sh->full[i], 1);
-            mbar_init(&sh->peer_full[i], 1);
             mbar_init(&sh->empty[i], 1);
         }
-        for (int i = 0; i < pl.n_slabs; ++i) {
-            mbar_init(&sh->a_full[i], 1);
-            mbar_init(&sh->peer_a_full[i], 1);
-            mbar_init(&sh->a_empty[i], 1);
+        for (int i = 0; i < n_abuf; ++i) {
+            mbar_init(&sh->as_full[i], 1);
+            mbar_init(&sh->as_empty[i], 1);
+        }
+        for (int i = 0; i < n_slabs; ++i) {
+            mbar_init(&sh->a_full[i], 2);
+            mbar_init(&sh->a_empty[i], a.n_tiles >= 2 ? 2 : 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&sh->acc_full[i], 1);
-            mbar_init(&sh->acc_empty[i], 8);  // 4 epilogue warps in each CTA
+            mbar_init(&sh->acc_empty[i], 8 * NSETS);
         }
         fence_mbar_init();
     }
-    for (int i = threadIdx.x; i < a.Nc; i += kGemmThreads) bias_s[i] = a.bias[i];
+    for (int i = threadIdx.x; i < a.Nc; i += kThreads) bias_s[i] = a.bias[i];
     if (warp == 2) tmem_alloc2<512>(&sh->tmem_base);
     tc_fence_before();
     __syncthreads();
-    cluster_sync();  // both CTAs' barriers and TMEM exist before any remote arrive / paired MMA
+    cluster_sync();  // both CTAs' barriers and TMEM exist before any remote arrive, remote complete_tx or paired MMA
     tc_fence_after();
     const uint32_t tmem = sh->tmem_base;
-    const int KS = pl.KS, n_slabs = pl.n_slabs, n_stages = pl.n_stages;
     const size_t a_tile_bytes = tile_bytes(a.K);
+    const uint32_t tA0 = tmem + 2u * (uint32_t)pl.acc_cols;  // A image: 8 columns per K-step
 
     if (warp == 0) {
-        // ===== producer: this CTA's A tile and its half of every weight stage =====
+        // ===== weight producer: this CTA's half (NT/2 rows) of every stage, bytes completed on the leader's barrier =====
         if (elect_one()) {
             uint32_t it = 0, st = 0, ph = 0, im = 0;
+            const uint32_t full_leader = mapa_u32(&sh->full[0], 0);
             for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
-                const int mt = 2 * mp + (int)rank;
-                const bool valid = mt < a.mt_count;  // an odd tile count leaves the last pair's second tile as padding
-                const int q = mt / a.T, t = mt % a.T;
-                const uint8_t *At = reinterpret_cast<const uint8_t *>(a.A) + (size_t)(q * a.A_q + t + a.A_t0) * a_tile_bytes;
                 for (int j = 0; j < a.n_tiles; ++j) {
-                    const int NH = a.nt_size[j] >> 1;  // rows of this CTA's half
-                    const uint8_t *Bt = reinterpret_cast<const uint8_t *>(a.B2) + a.nt_off[j] + (size_t)rank * NH * a.K * 2;
+                    const int NH = a.nt_size[j] >> 1;
+                    const void *tmap = &maps.m[2 * j + (int)rank];
+                    const uint32_t both = 2u * (uint32_t)(NH * 16) * (uint32_t)(2 * ks);  // the box is always whole (columns past K are zero-filled)
                     for (int sl = 0; sl < n_slabs; ++sl, ++it) {
-                        const int k0 = sl * KS, kw = min(KS, a.K - k0);
-                        if (j == 0) {
-                            mbar_wait_cluster(&sh->a_empty[sl], (im & 1) ^ 1);
-                            if (valid) {
-                                const uint32_t ab = (uint32_t)(kw / 8) * (kTileM * 16);
-                                mbar_expect_tx(&sh->a_full[sl], ab);
-                                bulk_g2s(sA + (size_t)(k0 / 8) * (kTileM * 16), At + (size_t)(k0 / 8) * (kTileM * 16), ab, &sh->a_full[sl]);
-                            } else {
-                                mbar_arrive(&sh->a_full[sl]);
-                            }
-                        }
-                        mbar_wait_cluster(&sh->empty[st], ph ^ 1);
-                        const uint32_t bb = (uint32_t)(kw / 8) * (NH * 16);
-                        mbar_expect_tx(&sh->full[st], bb);
-                        bulk_g2s(sB + (size_t)st * pl.stage_bytes, Bt + (size_t)(k0 / 8) * (NH * 16), bb, &sh->full[st]);
+                        mbar_wait(&sh->empty[st], ph ^ 1);
+                        if (leader) mbar_expect_tx(&sh->full[st], both);
+                        tma2_load_2d(sB + (size_t)st * pl.stage_bytes, tmap, full_leader + 8u * st, 0, sl * 2 * ks);
+                        PAIR_TRACE(0, im, j, sl);
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
                 }
@@ -108,75 +145,128 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) tc_
             // drain: the leader's multicast commits to this CTA's barriers must have landed before the CTA exits
             for (uint32_t s = 0; s < (uint32_t)n_stages && s < it; ++s) {
                 const uint32_t last = ((it - 1 - s) / n_stages) * n_stages + s;
-                mbar_wait_cluster(&sh->empty[s], (last / n_stages) & 1);
+                mbar_wait(&sh->empty[s], (last / n_stages) & 1);
             }
-            if (im) for (int sl = 0; sl < n_slabs; ++sl) mbar_wait_cluster(&sh->a_empty[sl], (im - 1) & 1);
         }
     } else if (warp == 3) {
-        // ===== relay (peer only): forward this CTA's operand arrivals to the leader, in the issuer's order =====
-        if (!leader && elect_one()) {
-            uint32_t st = 0, ph = 0, im = 0;
-            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im)
-                for (int j = 0; j < a.n_tiles; ++j)
-                    for (int sl = 0; sl < n_slabs; ++sl) {
-                        if (j == 0) {
-                            mbar_wait(&sh->a_full[sl], im & 1);
-                            mbar_arrive_cluster(&sh->peer_a_full[sl], 0);
-                        }
-                        mbar_wait(&sh->full[st], ph);
-                        mbar_arrive_cluster(&sh->peer_full[st], 0);
-                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
-                    }
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer (leader only): 256 x NT x 16 per instruction =====
-        if (leader && elect_one()) {
-            uint32_t st = 0, ph = 0, work = 0, im = 0;
-            const uint64_t ad0 = make_smem_desc(smem_u32(sA), kTileM * 16, 128);
-            const uint32_t alo0 = (uint32_t)ad0, ahi = (uint32_t)(ad0 >> 32);
-            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
-                for (int j = 0; j < a.n_tiles; ++j, ++work) {
-                    const int NT = a.nt_size[j], NH = NT >> 1;
-                    const uint32_t buf = work & 1;
-                    mbar_wait_cluster(&sh->acc_empty[buf], ((work >> 1) & 1) ^ 1);
-                    tc_fence_after();
-                    const uint32_t idesc = make_idesc_f16(2 * kTileM, NT);
-                    const uint32_t d = tmem + buf * 256;
-                    const bool last_n = (j == a.n_tiles - 1);
-                    const uint32_t bstep = 2u * (uint32_t)NH;  // one K-step of a half stage = 2 core columns = 2*NH*16 bytes
-                    for (int sl = 0; sl < n_slabs; ++sl) {
-                        if (j == 0) {
-                            mbar_wait(&sh->a_full[sl], im & 1);
-                            mbar_wait_cluster(&sh->peer_a_full[sl], im & 1);
-                        }
-                        mbar_wait(&sh->full[st], ph);
-                        mbar_wait_cluster(&sh->peer_full[st], ph);
-                        tc_fence_after();
-                        const int k0 = sl * KS, nk = min(KS, a.K - k0) / 16;
-                        const uint64_t bd0 = make_smem_desc(smem_u32(sB + (size_t)st * pl.stage_bytes), NH * 16, 128);
-                        const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
-                        const uint32_t alo = alo0 + (uint32_t)(k0 / 8) * (kTileM * 16 / 16);
-                        if (sl == 0) mma2_ss_lohi<false>(d, alo, ahi, blo, bhi, idesc);
-                        else mma2_ss_lohi<true>(d, alo, ahi, blo, bhi, idesc);
-#pragma unroll
-                        for (int kk = 1; kk < 4; ++kk)
-                            if (kk < nk) mma2_ss_lohi<true>(d, alo + kk * (2 * kTileM * 16 / 16), ahi, blo + kk * bstep, bhi, idesc);
-                        mma2_commit_mc(&sh->empty[st], 3);
-                        if (last_n) mma2_commit_mc(&sh->a_empty[sl], 3);
-                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
-                    }
-                    mma2_commit_mc(&sh->acc_full[buf], 3);
+        // ===== A producer: this CTA's own M-tile, slab by slab into the staging buffers =====
+        if (elect_one()) {
+            uint32_t ab = 0, abph = 0;
+            for (int mp = pair0; mp < n_mpairs; mp += pair_stride) {
+                const int mt = 2 * mp + (int)rank;
+                if (mt >= a.mt_count) continue;  // an odd tile count leaves the last pair's second tile as padding
+                const int q = mt / a.T, t = mt % a.T;
+                const uint8_t *At = reinterpret_cast<const uint8_t *>(a.A) + (size_t)(q * a.A_q + t + a.A_t0) * a_tile_bytes;
+                for (int sl = 0; sl < n_slabs; ++sl) {
+                    const int nk = min(ks, pl.nk_total - sl * ks);
+                    mbar_wait(&sh->as_empty[ab], abph ^ 1);
+                    const uint32_t bytes = (uint32_t)nk * (2u * kTileM * 16u);
+                    mbar_expect_tx(&sh->as_full[ab], bytes);
+                    bulk_g2s(sAst + (size_t)ab * pl.a_slab_bytes, At + (size_t)(sl * ks) * (2 * kTileM * 16), bytes, &sh->as_full[ab]);
+                    if (++ab == (uint32_t)n_abuf) { ab = 0; abph ^= 1; }
                 }
             }
         }
+    } else if (warp == 1 || warp == 2) {
+        // ===== MMA issuers (leader only): warp 1 takes the even N-tiles (accumulator 0), warp 2 the odd ones =====
+        // 256 x NT x 16 per instruction, A from each CTA's own TMEM.  The two threads own separate accumulators and
+        // separate ring stages (N-tile `work` uses stages [work*n_slabs, (work+1)*n_slabs) of the producer's sequence).
+        if (leader && elect_one()) {
+            const uint32_t me = warp == 1 ? 0u : 1u;
+            uint32_t st = 0, ph = 0, work = 0, im = 0;
+            const uint32_t d = tmem + me * (uint32_t)pl.acc_cols;
+            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+                for (int j = 0; j < a.n_tiles; ++j, ++work) {
+                    if ((work & 1u) != me) {  // the other issuer's N-tile: skip its stages
+                        st += (uint32_t)n_slabs;
+                        while (st >= (uint32_t)n_stages) { st -= (uint32_t)n_stages; ph ^= 1; }
+                        continue;
+                    }
+                    const int NT = a.nt_size[j], NH = NT >> 1;
+                    mbar_wait(&sh->acc_empty[me], ((work >> 1) & 1) ^ 1);
+                    tc_fence_after();
+                    PAIR_TRACE(4, im, j, 0);
+                    const uint32_t idesc = make_idesc_f16(2 * kTileM, NT);
+                    const bool first_mine = j <= 1;                 // this thread's first N-tile of the M-pair: the A slabs may still be arriving
+                    const bool frees_a = j >= a.n_tiles - 2;        // the M-pair's last N-tile of each issuer releases the A slabs
+                    const uint32_t bstep = 2u * (uint32_t)NH;       // one K-step of a half stage = 2 core columns = 2*NH*16 bytes
+                    for (int sl = 0; sl < n_slabs; ++sl) {
+                        if (first_mine) { mbar_wait(&sh->a_full[sl], im & 1); if (j == 0) PAIR_TRACE(3, im, 0, 2 + sl); }
+                        mbar_wait(&sh->full[st], ph);
+                        tc_fence_after();
+                        PAIR_TRACE(1, im, j, sl);
+                        const int nk = min(ks, pl.nk_total - sl * ks);
+                        const uint64_t bd0 = make_smem_desc(smem_u32(sB + (size_t)st * pl.stage_bytes), NH * 16, 128);
+                        const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
+                        const uint32_t ta = tA0 + (uint32_t)(sl * ks) * 8u;
+                        if (sl == 0) mma2_ts_lohi<false>(d, ta, blo, bhi, idesc);
+                        else mma2_ts_lohi<true>(d, ta, blo, bhi, idesc);
+#pragma unroll
+                        for (int kk = 1; kk < 8; ++kk)
+                            if (kk < nk) mma2_ts_lohi<true>(d, ta + kk * 8u, blo + kk * bstep, bhi, idesc);
+                        mma2_commit_mc(&sh->empty[st], 3);                 // the stage is free in both CTAs once these MMAs have read it
+                        if (frees_a) mma2_commit_mc(&sh->a_empty[sl], 3);  // and (with the other issuer's commit) so are this A slab's TMEM columns
+                        PAIR_TRACE(2, im, j, sl);
+                        if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
+                    }
+                    mma2_commit_mc(&sh->acc_full[me], 3);
+                    PAIR_TRACE(4, im, j, 1);
+                }
+            }
+        }
+    } else if (warp >= 8 && warp < 12) {
+        // ===== A stagers: staging buffer -> TMEM, thread = row (lane quadrant = warp % 4) =====
+        const int row = (warp & 3) * 32 + lane;
+        const uint32_t tA = tA0 + ((uint32_t)((warp & 3) * 32) << 16);
+        const uint32_t a_full_leader = mapa_u32(&sh->a_full[0], 0);
+        uint32_t ab = 0, abph = 0, im = 0;
+        for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+            const bool valid = 2 * mp + (int)rank < a.mt_count;
+            for (int sl = 0; sl < n_slabs; ++sl) {
+                const int nk = min(ks, pl.nk_total - sl * ks);
+                mbar_wait(&sh->a_empty[sl], (im & 1) ^ 1);  // the previous M-tile's MMAs over these columns are done
+                tc_fence_after();
+                if (warp == 8 && lane == 0) PAIR_TRACE(4, im, 0, 2 + sl);
+                if (valid) {
+                    mbar_wait(&sh->as_full[ab], abph);
+                    if (warp == 8 && lane == 0) PAIR_TRACE(4, im, 1, 2 + sl);
+                    const uint8_t *src = sAst + (size_t)ab * pl.a_slab_bytes + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        if (kk < nk) {
+                            const uint4 lo = *reinterpret_cast<const uint4 *>(src + (size_t)(2 * kk) * (kTileM * 16));
+                            const uint4 hi = *reinterpret_cast<const uint4 *>(src + (size_t)(2 * kk + 1) * (kTileM * 16));
+                            const uint32_t r[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+                            tmem_st8(tA + (uint32_t)(sl * ks + kk) * 8u, r);
+                        }
+                    }
+                    tmem_wait_st();
+                }
+                if (warp == 8 && lane == 0) PAIR_TRACE(4, im, 3, 2 + sl);
+                tc_fence_before();
+                bar_sync(1, 128);
+                if (warp == 8 && lane == 0) {
+                    if (valid) mbar_arrive(&sh->as_empty[ab]);
+                    mbar_arrive_addr(a_full_leader + 8u * (uint32_t)sl);
+                    PAIR_TRACE(4, im, 2, 2 + sl);
+                }
+                if (valid && ++ab == (uint32_t)n_abuf) { ab = 0; abph ^= 1; }
+            }
+        }
+        // drain the leader's last multicast commits to this CTA's a_empty barriers
+        if (im) for (int sl = 0; sl < n_slabs; ++sl) mbar_wait(&sh->a_empty[sl], (im - 1) & 1);
     } else if (warp >= 4) {
-        // ===== epilogue =====
+        // ===== epilogue (this CTA's 128 rows): warp set h takes the 32-column chunks with (c/32) % NSETS == h =====
         const int wq = warp & 3;
+        const int hset = warp >= 12 ? 1 : 0;
         const int row = wq * 32 + lane;
         const size_t c_tile_bytes = tile_bytes(a.Nc);
-        float *tr = reinterpret_cast<float *>(smem + pl.tr_off) + wq * (32 * 33);  // OUT == 1: this warp's 32x32 transpose pad
-        uint32_t work = 0;
-        int im = 0;
+        float *tr = reinterpret_cast<float *>(smem + pl.tr_off) + (hset * 4 + wq) * (32 * 33);  // OUT == 1: this warp's 32x32 transpose pad
+        uint32_t work = 0, im = 0;
+        const uint32_t acc_empty_leader = mapa_u32(&sh->acc_empty[0], 0);
+        uint8_t *Ct = nullptr;
+        float *g0 = nullptr;   // OUT == 1: gains row of this warp's first sequence
+        int rows_valid = 0;
 
         // bias + activation of 8 consecutive columns starting at column `col` (absolute, multiple of 8)
         auto act8 = [&](const uint32_t *r, int col, float (&v)[8]) {
@@ -190,14 +280,55 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) tc_
                 v[i] = x;
             }
         };
+        // one chunk of up to 32 accumulator columns (ng groups of 8), absolute first column `col`
+        auto emit = [&](const uint32_t (&r)[32], int col, int ng) {
+            if (OUT == 0) {
+#pragma unroll
+                for (int gI = 0; gI < 4; ++gI) {
+                    if (gI < ng) {
+                        float v[8];
+                        act8(r + 8 * gI, col + 8 * gI, v);
+                        uint4 o;
+                        o.x = pack_h2(v[0], v[1]); o.y = pack_h2(v[2], v[3]); o.z = pack_h2(v[4], v[5]); o.w = pack_h2(v[6], v[7]);
+                        *reinterpret_cast<uint4 *>(Ct + (size_t)((col >> 3) + gI) * (kTileM * 16)) = o;
+                    }
+                }
+            } else {
+                // thread = row: park the 32 columns in shared memory, then every lane writes one column of each
+                // row so a row's 32 floats leave as one 128-byte store
+#pragma unroll
+                for (int gI = 0; gI < 4; ++gI) {
+                    if (gI < ng) {
+                        float v[8];
+                        act8(r + 8 * gI, col + 8 * gI, v);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) tr[lane * 33 + 8 * gI + i] = v[i];
+                    }
+                }
+                __syncwarp();
+                const int cl = col + lane;
+                if (cl < a.n_valid && lane < 8 * ng) {
+                    float *gp = g0 + cl;
+                    for (int rr = 0; rr < rows_valid; ++rr) gp[(size_t)rr * (kFrames * kBins)] = tr[rr * 33 + lane];
+                }
+                __syncwarp();
+            }
+        };
+        auto load = [&](uint32_t taddr, int c, int NT, uint32_t (&r)[32]) {
+            if (c + 32 <= NT) {
+                tmem_ld32(taddr + c, r);
+            } else {  // N-tiles are multiples of 16
+                uint32_t r16[16];
+                tmem_ld16(taddr + c, r16);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) { r[i] = r16[i]; r[16 + i] = 0; }
+            }
+        };
 
         for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
             const int mt = 2 * mp + (int)rank;
             const bool valid = mt < a.mt_count;
             const int q = mt / a.T, t = mt % a.T;
-            uint8_t *Ct = nullptr;
-            float *g0 = nullptr;   // OUT == 1: gains row of this warp's first sequence
-            int rows_valid = 0;
             if (OUT == 0) {
                 Ct = reinterpret_cast<uint8_t *>(a.C) + (size_t)(q * a.C_q + t + a.C_t0) * c_tile_bytes +
                      (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16;
@@ -211,59 +342,40 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) tc_
             for (int j = 0; j < a.n_tiles; ++j, ++work) {
                 const int NT = a.nt_size[j], col0 = a.nt_col[j];
                 const uint32_t buf = work & 1;
-                mbar_wait_cluster(&sh->acc_full[buf], (work >> 1) & 1);
+                mbar_wait(&sh->acc_full[buf], (work >> 1) & 1);
                 tc_fence_after();
-                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 0);
-                const uint32_t tbase = tmem + buf * 256 + ((uint32_t)(wq * 32) << 16);
-                for (int c = 0; c < (valid ? NT : 0); c += 32) {
-                    uint32_t r[32];
-                    const bool full32 = c + 32 <= NT;  // N-tiles are multiples of 16
-                    if (full32) {
-                        tmem_ld32(tbase + c, r);
-                    } else {
-                        uint32_t r16[16];
-                        tmem_ld16(tbase + c, r16);
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) { r[i] = r16[i]; r[16 + i] = 0; }
-                    }
+                if (warp == 4 && lane == 0) PAIR_TRACE(3, im, j, 0);
+                const uint32_t tbase = tmem + buf * (uint32_t)pl.acc_cols + ((uint32_t)(wq * 32) << 16);
+                // The loads run one chunk ahead of the arithmetic (tcgen05.wait::ld covers every load issued so far, so the
+                // next chunk's load is issued right after the wait for the current one), and the accumulator goes back to
+                // the MMA issuer as soon as this warp's last chunk sits in registers.
+                const int NTv = valid ? NT : 0;
+                constexpr int kStride = 32 * NSETS;
+                uint32_t rA[32], rB[32];
+                int c = hset * 32;
+                bool released = false;
+                auto release = [&]() {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_addr(acc_empty_leader + 8u * buf);
+                    released = true;
+                };
+                if (c < NTv) load(tbase, c, NT, rA);
+                while (c < NTv) {
                     tmem_wait_ld();
-                    const int ng = full32 ? 4 : 2;  // groups of 8 columns
-                    if (OUT == 0) {
-#pragma unroll
-                        for (int gI = 0; gI < 4; ++gI) {
-                            if (gI < ng) {
-                                float v[8];
-                                act8(r + 8 * gI, col0 + c + 8 * gI, v);
-                                uint4 o;
-                                o.x = pack_h2(v[0], v[1]); o.y = pack_h2(v[2], v[3]); o.z = pack_h2(v[4], v[5]); o.w = pack_h2(v[6], v[7]);
-                                *reinterpret_cast<uint4 *>(Ct + (size_t)(((col0 + c) >> 3) + gI) * (kTileM * 16)) = o;
-                            }
-                        }
-                    } else {
-                        // thread = row: park the 32 columns in shared memory, then every lane writes one column of each
-                        // row so a row's 32 floats leave as one 128-byte store
-#pragma unroll
-                        for (int gI = 0; gI < 4; ++gI) {
-                            if (gI < ng) {
-                                float v[8];
-                                act8(r + 8 * gI, col0 + c + 8 * gI, v);
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) tr[lane * 33 + 8 * gI + i] = v[i];
-                            }
-                        }
-                        __syncwarp();
-                        const int col = col0 + c + lane;
-                        if (col < a.n_valid && lane < 8 * ng) {
-                            float *gp = g0 + col;
-                            for (int rr = 0; rr < rows_valid; ++rr) gp[(size_t)rr * (kFrames * kBins)] = tr[rr * 33 + lane];
-                        }
-                        __syncwarp();
-                    }
+                    int c2 = c + kStride;
+                    if (c2 < NTv) load(tbase, c2, NT, rB); else release();
+                    emit(rA, col0 + c, c + 32 <= NT ? 4 : 2);
+                    c = c2;
+                    if (c >= NTv) break;
+                    tmem_wait_ld();
+                    c2 = c + kStride;
+                    if (c2 < NTv) load(tbase, c2, NT, rA); else release();
+                    emit(rB, col0 + c, c + 32 <= NT ? 4 : 2);
+                    c = c2;
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (wq == 0 && lane == 0) GEMM_TRACE(3, im, j, 1);
-                if (lane == 0) mbar_arrive_cluster(&sh->acc_empty[buf], 0);
+                if (!released) release();
+                if (warp == 4 && lane == 0) PAIR_TRACE(3, im, j, 1);
             }
         }
     }
@@ -273,48 +385,100 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1) tc_
     if (warp == 2) tmem_dealloc2<512>(tmem);
 }
 
-}  // namespace
-
-template <int ACT, int OUT>
-static void launch_variant2(const GemmArgs &a, const GemmPlan &pl, int grid, cudaStream_t s) {
-    static bool attr = false;
-    if (!attr) {
-        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm2_kernel<ACT, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-        attr = true;
+// cuTensorMapEncodeTiled through the runtime (the library does not link libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        FVAD_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !p) throw Error(FVAD_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+        fn = reinterpret_cast<EncodeTiledFn>(p);
     }
-    tc_gemm2_kernel<ACT, OUT><<<grid, kGemmThreads, pl.smem_bytes, s>>>(a, pl);
+    return fn;
 }
 
-void launch_tc_gemm2(const GemmArgs &a, int n_sm, cudaStream_t s) {
+}  // namespace
+
+// K-steps per weight slab of the pair kernel: equal pieces of at most 8 K-steps (the issue loop's unroll)
+int pair_slab_ksteps(int K) {
+    const int nk = K / 16;
+    const int n_slabs = (nk + 7) / 8;
+    return (nk + n_slabs - 1) / n_slabs;
+}
+
+// Tensor maps of a layer's CTA-pair weight image: N-tile j, half r = a [K/8 core columns][NT/2 rows x 16 B] array at
+// img2 + nt_off[j] + r * (NT/2)*K*2; one box = the (NT/2 rows) x (ks K-steps) piece a CTA stores of a weight stage.
+void build_pair_maps(PairMaps &maps, const void *img2, int K, int n_tiles, const int *nt_size, const unsigned *nt_off) {
+    const int ks = pair_slab_ksteps(K);
+    for (int j = 0; j < n_tiles; ++j)
+        for (int r = 0; r < 2; ++r) {
+            const int NH = nt_size[j] / 2;
+            if (nt_size[j] % 16 || NH % 8 || NH * 2 > 256) throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: N-tile must be a multiple of 16, at most 256");
+            void *base = const_cast<uint8_t *>(static_cast<const uint8_t *>(img2)) + nt_off[j] + (size_t)r * NH * K * 2;
+            const cuuint64_t gdim[2] = {(cuuint64_t)NH * 2, (cuuint64_t)K / 8};  // 8-byte elements: a core column is NH*16 bytes
+            const cuuint64_t gstr[1] = {(cuuint64_t)NH * 16};
+            const cuuint32_t box[2] = {(cuuint32_t)NH * 2, (cuuint32_t)(2 * ks)};
+            const cuuint32_t estr[2] = {1, 1};
+            const CUresult rc = encode_tiled()(&maps.m[2 * j + r], CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, base, gdim, gstr, box, estr,
+                                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (rc != CUDA_SUCCESS) throw Error(FVAD_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)rc) + ")");
+        }
+}
+
+template <int ACT, int OUT, int NSETS>
+static void launch_pair_variant(const GemmArgs &a, const PairPlan &pl, const PairMaps &maps, int grid, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) {
+        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_pair_kernel<ACT, OUT, NSETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        attr = true;
+    }
+    tc_gemm_pair_kernel<ACT, OUT, NSETS><<<grid, 384 + 128 * (NSETS - 1), pl.smem_bytes, s>>>(a, pl, maps);
+}
+
+void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStream_t s) {
     if (a.mt_count <= 0) return;
-    GemmPlan pl;
+    PairPlan pl;
     int nt_max = 0;
     for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
-    pl.a_bytes = a.K * 256;  // K/8 core columns x 2048 B
-    const int tr_bytes = a.out_mode == 1 ? 4 * 32 * 33 * 4 : 0;
-    static_assert(sizeof(GemmShared) <= 2048, "barrier block");
-    const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 2048;
-    pl.KS = 64;
-    for (;;) {
-        pl.stage_bytes = (nt_max / 2) * pl.KS * 2;  // this CTA's half of a weight stage
-        pl.n_stages = (kSmemTotal - pl.a_bytes - fixed) / pl.stage_bytes;
-        if (pl.n_stages >= 3 || pl.KS == 16) break;  // fewer, larger stages: the per-stage barrier round trip costs the issuing thread more than the shorter ring
-        pl.KS /= 2;
-    }
+    if (a.K % 16 || a.K / 2 + 2 * nt_max > 512)
+        throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: A tile + two accumulators exceed the 512 TMEM columns");
+    pl.nk_total = a.K / 16;
+    pl.ks = pair_slab_ksteps(a.K);
+    pl.n_slabs = (pl.nk_total + pl.ks - 1) / pl.ks;
+    pl.acc_cols = nt_max;
+    pl.stage_bytes = (nt_max / 2) * 16 * 2 * pl.ks;
+    pl.a_slab_bytes = pl.ks * 2 * kTileM * 16;
+    const int tr_bytes = a.out_mode == 1 ? 8 * 32 * 33 * 4 : 0;
+    static_assert(sizeof(PairShared) <= 1024, "barrier block");
+    const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 1024 + 16;
+    // A staging: a whole tile's slabs when that leaves the weight ring enough stages (timeline: with a buffer fewer the
+    // last slab's load starts only when the first buffer has been restaged and lands ~1 000 cycles late).
+    // Ring length: two issuers skip each other's stages and a parity wait can only tell "this fill" from "the fill
+    // before", so the fill before the one an issuer polls must be older than a stage that issuer has already consumed:
+    // n_stages >= n_slabs + 1 (one more for slack), and at least six for the L2 latency.
+    const int min_stages = pl.n_slabs + 2 > 6 ? pl.n_slabs + 2 : 6;
+    pl.n_abuf = pl.n_slabs < kMaxABuf ? pl.n_slabs : kMaxABuf;
+    while (pl.n_abuf > 2 && (kSmemTotal - pl.n_abuf * pl.a_slab_bytes - fixed) / pl.stage_bytes < min_stages) --pl.n_abuf;
+    pl.b_off = pl.n_abuf * pl.a_slab_bytes;
+    pl.n_stages = (kSmemTotal - pl.b_off - fixed) / pl.stage_bytes;
     if (pl.n_stages > kMaxStages) pl.n_stages = kMaxStages;
-    pl.n_slabs = (a.K + pl.KS - 1) / pl.KS;
-    if (pl.n_stages < 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: layer does not fit the shared-memory plan");
-    pl.bias_off = pl.a_bytes + pl.n_stages * pl.stage_bytes;
+    if (pl.n_stages < pl.n_slabs + 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: layer does not fit the shared-memory plan");
+    pl.bias_off = pl.b_off + pl.n_stages * pl.stage_bytes;
     pl.tr_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
-    pl.sh_off = pl.tr_off + tr_bytes;
-    pl.smem_bytes = pl.sh_off + 2048;
+    pl.sh_off = (pl.tr_off + tr_bytes + 15) & ~15;
+    pl.smem_bytes = pl.sh_off + 1024;
     const int n_mpairs = (a.mt_count + 1) / 2;
     const int grid = 2 * (n_mpairs < n_sm / 2 ? n_mpairs : n_sm / 2);
     if (a.out_mode == 1) {
         if (a.act != 2) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: the gains output applies the sigmoid");
-        launch_variant2<2, 1>(a, pl, grid, s);
-    } else if (a.act == 0) launch_variant2<0, 0>(a, pl, grid, s);
-    else if (a.act == 1) launch_variant2<1, 0>(a, pl, grid, s);
+        launch_pair_variant<2, 1, 2>(a, pl, maps, grid, s);
+    } else if (a.act == 0) launch_pair_variant<0, 0, 1>(a, pl, maps, grid, s);
+    else if (a.act == 1) launch_pair_variant<1, 0, 1>(a, pl, maps, grid, s);
     else throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: unsupported activation/output combination");
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());

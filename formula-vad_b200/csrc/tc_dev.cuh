@@ -108,6 +108,33 @@ __device__ __forceinline__ void bulk_g2s_mc(void *dst_smem, const void *src, uin
         : "memory");
 }
 
+// shared::cluster address of the variable at `p`'s offset in CTA `cta` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(const void *p, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(cta));
+    return r;
+}
+// Arrive on a barrier given by its shared::cluster address (local or remote CTA), default semantics (release at CTA
+// scope), like CUTLASS's ClusterBarrier::arrive(cta_id).  What these arrivals order across a CTA pair is tensor-memory
+// traffic, which the tcgen05 fences and waits around them cover; a `.release.cluster` here makes the arriving thread
+// drain its outstanding global stores first and a `.acquire.cluster` poll on the other side stalls the MMA issuer
+// until its own earlier MMAs retire (measured: the accumulator hand-over then costs a whole N-tile of tensor time,
+// which is what made the first pair kernels slower than one CTA).
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar_cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+}
+
+// TMA tile load (2-D tensor map) into THIS CTA's shared memory, completing its bytes on the barrier at shared::cluster
+// address `bar_cluster_addr` -- with .cta_group::2 that barrier may live in the peer CTA of the pair (the MMA leader), which
+// is what lets one tcgen05.mma.cta_group::2 issuer learn that both halves of an operand stage have landed without a relay.
+__device__ __forceinline__ void tma2_load_2d(void *dst_smem, const void *tmap, uint32_t bar_cluster_addr, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(tmap), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05
 template <uint32_t NCOLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t *slot_in_smem) {  // whole warp
