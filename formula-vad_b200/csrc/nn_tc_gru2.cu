@@ -96,14 +96,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
                 for (int t = 0; t < kSteps; ++t)
                     for (int c = 0; c < kChunks; ++c, ++it) {
                         const int st = it % kStages;
-                        mbar_wait_cluster(&sh->empty[st], ((it / kStages) & 1) ^ 1);
+                        mbar_wait(&sh->empty[st], ((it / kStages) & 1) ^ 1);
                         mbar_expect_tx(&sh->full[st], kHalfBytes);
                         bulk_g2s(smem + st * kHalfBytes, R + (size_t)c * (2 * kHalfBytes), kHalfBytes, &sh->full[st]);
                     }
             // drain: the leader's multicast commits to this CTA's `empty` barriers must have landed before exit
             for (uint32_t s = 0; s < (uint32_t)kStages && s < n_fill; ++s) {
                 const uint32_t last = ((n_fill - 1 - s) / kStages) * kStages + s;  // last fill of stage s
-                mbar_wait_cluster(&sh->empty[s], (last / kStages) & 1);
+                mbar_wait(&sh->empty[s], (last / kStages) & 1);
             }
         }
     } else if (warp == 3) {
@@ -112,7 +112,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
             for (uint32_t it = 0; it < n_fill; ++it) {
                 const int st = it % kStages;
                 mbar_wait(&sh->full[st], (it / kStages) & 1);
-                mbar_arrive_cluster(&sh->peer_full[st], 0);
+                mbar_arrive_addr(mapa_u32(&sh->peer_full[st], 0));
             }
         }
     } else if (warp == 1) {
@@ -122,16 +122,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
             uint32_t it = 0, step = 0, use[2] = {0, 0};
             for (int ip = 0; ip < n_p; ++ip)
                 for (int t = 0; t < kSteps; ++t, ++step) {
-                    mbar_wait_cluster(&sh->h_ready, step & 1);  // h_{t-1} complete in both CTAs' TMEM
+                    mbar_wait(&sh->h_ready, step & 1);  // h_{t-1} complete in both CTAs' TMEM
                     tc_fence_after();
                     const uint32_t hold = tmem + ((t & 1) ? kColH1 : kColH0);
                     for (int c = 0; c < kChunks; ++c, ++it) {
                         const uint32_t g = c & 1;
-                        mbar_wait_cluster(&sh->acc_empty[g], (use[g] & 1) ^ 1);
+                        mbar_wait(&sh->acc_empty[g], (use[g] & 1) ^ 1);
                         ++use[g];
                         const int st = it % kStages;
                         mbar_wait(&sh->full[st], (it / kStages) & 1);
-                        mbar_wait_cluster(&sh->peer_full[st], (it / kStages) & 1);
+                        mbar_wait(&sh->peer_full[st], (it / kStages) & 1);
                         tc_fence_after();
                         const uint32_t d = tmem + (g ? kColAcc1 : kColAcc0);
                         // K-step kk: h columns [8kk, 8kk+8); R slab 2 core columns = 2*24*16 B = 48 descriptor units on
@@ -165,7 +165,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive_cluster(&sh->h_ready, 0);
+                if (lane == 0) mbar_arrive_addr(mapa_u32(&sh->h_ready, 0));
             }
             for (int t = 0; t < kSteps; ++t) {
                 const uint32_t hold = tmem + lane_off + ((t & 1) ? kColH1 : kColH0);
@@ -186,7 +186,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
                         for (int i = 0; i < 6; ++i)
                             xn[i] = __ldg(reinterpret_cast<const uint4 *>(xpt + (size_t)((c + 2) * 6 + i) * (kTileM * 16)));
                     }
-                    mbar_wait_cluster(&sh->acc_full[g], use & 1);
+                    mbar_wait(&sh->acc_full[g], use & 1);
                     ++use;
                     tc_fence_after();
                     uint32_t az[16], ar[16], an[16], ho[8];
@@ -197,7 +197,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
                     tmem_wait_ld();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive_cluster(&sh->acc_empty[g], 0);  // drained: the pair's next chunk may overwrite it
+                    if (lane == 0) mbar_arrive_addr(mapa_u32(&sh->acc_empty[g], 0));  // drained: the pair's next chunk may overwrite it
 
                     const uint32_t *xw = reinterpret_cast<const uint32_t *>(x);  // 24 words: z[0..7] r[8..15] n[16..23] (pairs)
                     uint32_t hn[8];
@@ -227,7 +227,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1) tc_
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0 && t < kSteps - 1) mbar_arrive_cluster(&sh->h_ready, 0);  // the next pair's zero fill arrives for its t = 0
+                if (lane == 0 && t < kSteps - 1) mbar_arrive_addr(mapa_u32(&sh->h_ready, 0));  // the next pair's zero fill arrives for its t = 0
             }
         }
     }
