@@ -60,6 +60,7 @@ struct Layer {  // one dense layer prepared for launch_tc_gemm
     int K = 0, Nc = 0, n_valid = 0, n_tiles = 0;
     int a_tmem = 0;  // GemmArgs::a_tmem for this layer (the N-tiles were cut for it)
     tc::PairMaps maps;  // CTA-pair kernel: tensor maps over img2 (built when the layer runs on pairs)
+    bool pair = false;  // runs on CTA pairs (nn_tc_gemm2.cu)
     int nt_size[tc::kMaxNTiles] = {}, nt_col[tc::kMaxNTiles] = {};
     unsigned nt_off[tc::kMaxNTiles] = {};
 };
@@ -110,6 +111,7 @@ void build_layer(Layer &L, const float *W, const float *bias, const int *perm, i
     L.bias.ensure(b.size());
     FVAD_CUDA_CHECK(cudaMemcpy(L.bias.p, b.data(), b.size() * sizeof(float), cudaMemcpyHostToDevice));
     memset(&L.maps, 0, sizeof(L.maps));
+    L.pair = pair;
     if (pair) tc::build_pair_maps(L.maps, L.img2.p, Kp, L.n_tiles, L.nt_size, L.nt_off);
 }
 
@@ -127,7 +129,6 @@ public:
         if (const char *e = getenv("FVAD_NN_TIMING")) timing_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_GEMM_PAIR")) gemm_pair_ = atoi(e) != 0;
         if (const char *e = getenv("FVAD_GEMM_TS")) gemm_ts_ = atoi(e) != 0;
-        if (gemm_pair_) gemm_ts_ = false;
         // N-tiles: with the A tile in TMEM (K/2 columns) the two accumulators share what is left of the 512 columns
         const bool ts = gemm_ts_;
         using T = std::vector<int>;
@@ -137,14 +138,22 @@ public:
         for (int c = 0; c < 25; ++c)
             for (int g = 0; g < 3; ++g)
                 for (int u = 0; u < 16; ++u) perm[(size_t)(48 * c + 16 * g + u)] = g * H + 16 * c + u;
-        const bool gp = gemm_pair_;
-        build_layer(fc1_, w.fc1_w.data(), w.fc1_b.data(), nullptr, H, 161, 176, {208, 192}, gp);
+        // which layers run on CTA pairs (FVAD_GEMM_PAIR_MASK, A/B and bisecting): 1 fc1, 2 W1/W2, 4 fc2, 8 fc3, 16 fc4
+        int pmask = gemm_pair_ ? 30 : 0;  // (fc1: K = 176 makes it accumulator-drain bound either way; one CTA is as fast)
+        if (const char *e = getenv("FVAD_GEMM_PAIR_MASK")) pmask = atoi(e);
+        bool gp = (pmask & 1) != 0;
+        // CTA pairs (nn_tc_gemm2.cu): every layer's A tile in TMEM (K/2 columns); N-tiles of 96 leave room for three
+        // accumulators at K = 400 (the layers whose accumulator drain runs as fast as their MMAs); the short tile comes
+        // FIRST so that the M-pair's last N-tile is a long one and the next tile's A slabs restage under it
+        build_layer(fc1_, w.fc1_w.data(), w.fc1_b.data(), nullptr, H, 161, 176, T{208, 192}, gp);
         for (int l = 0; l < 2; ++l) {
             // xp bias: Wb + Rb for z and r; Wb alone for n (Rb_n is applied inside r*(.), nn_tc_gru.cu)
             std::vector<float> b(3 * H);
             for (int i = 0; i < 3 * H; ++i) b[(size_t)i] = w.gru_Wb[l][(size_t)i] + (i < 2 * H ? w.gru_Rb[l][(size_t)i] : 0.0f);
+            gp = (pmask & 2) != 0;
             build_layer(gW_[l], w.gru_W[l].data(), b.data(), perm.data(), 3 * H, H, H,
-                        (ts || gp) ? T{144, 144, 144, 144, 144, 144, 144, 144, 48} : T{240, 240, 240, 240, 240}, gp);
+                        gp ? T{48, 144, 144, 144, 144, 144, 144, 144, 144}
+                           : ts ? T{144, 144, 144, 144, 144, 144, 144, 144, 48} : T{240, 240, 240, 240, 240}, gp);
             // R: 25 chunk images of 48 rows = one "layer" with 25 N-tiles of 48
             Layer tmp;
             std::vector<__half> img((size_t)3 * H * H);
@@ -169,10 +178,12 @@ public:
             gRbn_[l].ensure((size_t)H);
             FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
         }
-        // CTA pairs keep every layer's A tile in TMEM (K/2 columns): N-tiles of at most (512 - K/2)/2 columns, multiples of 16
-        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, gp ? T{128, 128, 128, 112, 112} : T{208, 208, 192}, gp);
-        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, gp ? T{96, 96, 96, 96, 96, 96, 32} : T{208, 208, 192}, gp);
-        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, (ts || gp) ? T{96, 80} : T{176}, gp);
+        gp = (pmask & 4) != 0;
+        build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, gp ? T{112, 112, 128, 128, 128} : T{208, 208, 192}, gp);
+        gp = (pmask & 8) != 0;
+        build_layer(fc3_, w.fc3_w.data(), w.fc3_b.data(), nullptr, 600, 600, 608, gp ? T{32, 96, 96, 96, 96, 96, 96} : T{208, 208, 192}, gp);
+        gp = (pmask & 16) != 0;
+        build_layer(fc4_, w.fc4_w.data(), w.fc4_b.data(), nullptr, 161, 600, 608, gp ? T{80, 96} : ts ? T{96, 80} : T{176}, gp);
         // A in TMEM caps the N-tile at (512 - K/2)/2 columns: 144 at K = 400, 96 at K = 608.  Measured per 20 stream-hours:
         // fc1 2.12 -> 1.75 ms, W1/W2 8.6 -> 7.5, fc4 3.43 -> 3.2; fc2 unchanged (4.0) and fc3 (K = 608, N-tile 96) 7.3 -> 8.8,
         // so those two keep A in shared memory with N-tiles of 208
@@ -268,7 +279,7 @@ private:
     bool traced_ = false;
     bool pair_ = false;
     bool gemm_ts_ = true;     // A tile in TMEM (FVAD_GEMM_TS=0: resident in shared memory, the first design)
-    bool gemm_pair_ = false;  // CTA-pair GEMM (FVAD_GEMM_PAIR=1): parity-green but 50 % slower than the one-CTA kernel, kept for A/B
+    bool gemm_pair_ = true;   // CTA-pair GEMM (nn_tc_gemm2.cu) for W1/W2/fc2/fc3/fc4; FVAD_GEMM_PAIR=0: every layer on the one-CTA kernel (A/B)
 
     void gru(int l, __half *hout, int Q, int t_store_min, cudaStream_t s) {
         unsigned long long *tr = nullptr;
@@ -299,7 +310,7 @@ private:
         return g;
     }
     void launch(const GemmArgs &g, const Layer &L, cudaStream_t s) {
-        if (gemm_pair_) tc::launch_tc_gemm2(g, L.maps, n_sm_, s);
+        if (L.pair) tc::launch_tc_gemm2(g, L.maps, n_sm_, s);
         else tc::launch_tc_gemm(g, n_sm_, s);
     }
     void gemm(const Layer &L, const __half *A, __half *C, int Q, int T, int A_q, int A_t0, int C_q, int C_t0, int act, cudaStream_t s) {

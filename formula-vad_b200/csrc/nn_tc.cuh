@@ -9,7 +9,7 @@ namespace fvad {
 namespace tc {
 
 constexpr int kTileM = 128;            // rows (sequences) per M-tile = TMEM lanes
-constexpr int kMaxNTiles = 12;
+constexpr int kMaxNTiles = 13;
 
 // bytes of one activation tile of `cols` columns (cols % 16 == 0) in the core-matrix tiled layout
 __host__ __device__ constexpr size_t tile_bytes(int cols) { return (size_t)kTileM * cols * 2; }

@@ -64,9 +64,10 @@ struct PairShared {
     uint64_t as_empty[kMaxABuf];  // per CTA: the stagers have moved it to TMEM
     uint64_t a_full[kMaxSlabs];   // LEADER's: A slab sl is in TMEM in BOTH CTAs (2 arrivals)
     uint64_t a_empty[kMaxSlabs];  // per CTA: the MMAs of the M-pair's last two N-tiles (one per issuer) over TMEM slab sl are done
-    uint64_t acc_full[2];         // per CTA: accumulator complete (multicast commit)
-    uint64_t acc_empty[2];        // LEADER's: drained by the epilogue warps of both CTAs (8 * NSETS arrivals)
+    uint64_t acc_full[3];         // per CTA: accumulator complete (multicast commit)
+    uint64_t acc_empty[3];        // LEADER's: drained by the epilogue warps of both CTAs (8 * NSETS arrivals)
     uint32_t tmem_base;
+    uint32_t passed[2];           // LEADER's: per MMA issuer, 1 + the last slab (producer's sequence) whose full-wait it has passed
 };
 
 struct PairPlan {  // host-computed (launch_tc_gemm2)
@@ -76,11 +77,12 @@ struct PairPlan {  // host-computed (launch_tc_gemm2)
     int stage_bytes;    // per CTA: max over N-tiles of (NT/2 rows) x (ks K-steps) fp16
     int a_slab_bytes;   // 128 rows x ks K-steps fp16
     int b_off, bias_off, tr_off, sh_off, smem_bytes;
-    int acc_cols;       // TMEM columns between the two accumulators (max NT); A starts at 2*acc_cols
+    int acc_cols;       // TMEM columns between accumulators (max NT)
+    int n_acc;          // accumulators: 3 when 3*acc_cols + K/2 <= 512 (N-tile `work` uses accumulator work % n_acc), else 2; A follows them
 };
 
 template <int ACT, int OUT, int NSETS>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS - 1), 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS - 1), 1) __maxnreg__(NSETS == 2 ? 112 : 128)
     tc_gemm_pair_kernel(const GemmArgs a, const PairPlan pl, const __grid_constant__ PairMaps maps) {
     constexpr int kThreads = 384 + 128 * (NSETS - 1);
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -107,10 +109,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
             mbar_init(&sh->a_full[i], 2);
             mbar_init(&sh->a_empty[i], a.n_tiles >= 2 ? 2 : 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < pl.n_acc; ++i) {
             mbar_init(&sh->acc_full[i], 1);
             mbar_init(&sh->acc_empty[i], 8 * NSETS);
         }
+        sh->passed[0] = sh->passed[1] = 0;
         fence_mbar_init();
     }
     for (int i = threadIdx.x; i < a.Nc; i += kThreads) bias_s[i] = a.bias[i];
@@ -121,7 +124,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
     tc_fence_after();
     const uint32_t tmem = sh->tmem_base;
     const size_t a_tile_bytes = tile_bytes(a.K);
-    const uint32_t tA0 = tmem + 2u * (uint32_t)pl.acc_cols;  // A image: 8 columns per K-step
+    const uint32_t tA0 = tmem + (uint32_t)(pl.n_acc * pl.acc_cols);  // A image: 8 columns per K-step
+    const uint32_t n_acc = (uint32_t)pl.n_acc;
 
     if (warp == 0) {
         // ===== weight producer: this CTA's half (NT/2 rows) of every stage, bytes completed on the leader's barrier =====
@@ -168,13 +172,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
             }
         }
     } else if (warp == 1 || warp == 2) {
-        // ===== MMA issuers (leader only): warp 1 takes the even N-tiles (accumulator 0), warp 2 the odd ones =====
-        // 256 x NT x 16 per instruction, A from each CTA's own TMEM.  The two threads own separate accumulators and
-        // separate ring stages (N-tile `work` uses stages [work*n_slabs, (work+1)*n_slabs) of the producer's sequence).
+        // ===== MMA issuers (leader only): warp 1 takes the even N-tiles, warp 2 the odd ones =====
+        // 256 x NT x 16 per instruction, A from each CTA's own TMEM.  N-tile `work` accumulates into buffer work % n_acc
+        // and uses ring stages [work*n_slabs, (work+1)*n_slabs) of the producer's sequence, so the two threads never
+        // share an accumulator or a stage.
         if (leader && elect_one()) {
             const uint32_t me = warp == 1 ? 0u : 1u;
+            // One ring, consumed by two threads that skip each other's stages.  A parity wait can only tell "this fill" from
+            // "the fill before", so before polling a stage whose previous fill belonged to the other issuer's N-tile this
+            // thread makes sure the other one has seen that fill land (sh->passed[]: slabs whose full-wait it has passed).
+            // The previous fill of slab (work, sl) is n_stages slabs back: N-tile work - q - (sl < rr).
+            const uint32_t q = (uint32_t)(n_stages / n_slabs), rr = (uint32_t)(n_stages % n_slabs);
+            volatile uint32_t *passed_me = &sh->passed[me], *passed_other = &sh->passed[me ^ 1u];
             uint32_t st = 0, ph = 0, work = 0, im = 0;
-            const uint32_t d = tmem + me * (uint32_t)pl.acc_cols;
             for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
                 for (int j = 0; j < a.n_tiles; ++j, ++work) {
                     if ((work & 1u) != me) {  // the other issuer's N-tile: skip its stages
@@ -183,7 +193,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                         continue;
                     }
                     const int NT = a.nt_size[j], NH = NT >> 1;
-                    mbar_wait(&sh->acc_empty[me], ((work >> 1) & 1) ^ 1);
+                    const uint32_t buf = work % n_acc, use = work / n_acc;
+                    const uint32_t d = tmem + buf * (uint32_t)pl.acc_cols;
+                    mbar_wait(&sh->acc_empty[buf], (use & 1) ^ 1);
                     tc_fence_after();
                     PAIR_TRACE(4, im, j, 0);
                     const uint32_t idesc = make_idesc_f16(2 * kTileM, NT);
@@ -192,7 +204,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                     const uint32_t bstep = 2u * (uint32_t)NH;       // one K-step of a half stage = 2 core columns = 2*NH*16 bytes
                     for (int sl = 0; sl < n_slabs; ++sl) {
                         if (first_mine) { mbar_wait(&sh->a_full[sl], im & 1); if (j == 0) PAIR_TRACE(3, im, 0, 2 + sl); }
+                        {
+                            const uint32_t back = q + ((uint32_t)sl < rr ? 1u : 0u);  // N-tiles between this slab and its stage's previous fill
+                            const uint32_t idx = work * (uint32_t)n_slabs + (uint32_t)sl;  // this slab in the producer's sequence
+                            if ((back & 1u) && idx >= (uint32_t)n_stages) {
+                                while (*passed_other <= idx - (uint32_t)n_stages) {}
+                                __threadfence_block();
+                            }
+                        }
                         mbar_wait(&sh->full[st], ph);
+                        __threadfence_block();
+                        *passed_me = work * (uint32_t)n_slabs + (uint32_t)sl + 1u;
                         tc_fence_after();
                         PAIR_TRACE(1, im, j, sl);
                         const int nk = min(ks, pl.nk_total - sl * ks);
@@ -209,7 +231,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                         PAIR_TRACE(2, im, j, sl);
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
-                    mma2_commit_mc(&sh->acc_full[me], 3);
+                    mma2_commit_mc(&sh->acc_full[buf], 3);
                     PAIR_TRACE(4, im, j, 1);
                 }
             }
@@ -341,8 +363,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
             }
             for (int j = 0; j < a.n_tiles; ++j, ++work) {
                 const int NT = a.nt_size[j], col0 = a.nt_col[j];
-                const uint32_t buf = work & 1;
-                mbar_wait(&sh->acc_full[buf], (work >> 1) & 1);
+                const uint32_t buf = work % n_acc;
+                mbar_wait(&sh->acc_full[buf], (work / n_acc) & 1);
                 tc_fence_after();
                 if (warp == 4 && lane == 0) PAIR_TRACE(3, im, j, 0);
                 const uint32_t tbase = tmem + buf * (uint32_t)pl.acc_cols + ((uint32_t)(wq * 32) << 16);
@@ -351,7 +373,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                 // the MMA issuer as soon as this warp's last chunk sits in registers.
                 const int NTv = valid ? NT : 0;
                 constexpr int kStride = 32 * NSETS;
-                uint32_t rA[32], rB[32];
                 int c = hset * 32;
                 bool released = false;
                 auto release = [&]() {
@@ -360,19 +381,30 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                     if (lane == 0) mbar_arrive_addr(acc_empty_leader + 8u * buf);
                     released = true;
                 };
-                if (c < NTv) load(tbase, c, NT, rA);
-                while (c < NTv) {
-                    tmem_wait_ld();
-                    int c2 = c + kStride;
-                    if (c2 < NTv) load(tbase, c2, NT, rB); else release();
-                    emit(rA, col0 + c, c + 32 <= NT ? 4 : 2);
-                    c = c2;
-                    if (c >= NTv) break;
-                    tmem_wait_ld();
-                    c2 = c + kStride;
-                    if (c2 < NTv) load(tbase, c2, NT, rA); else release();
-                    emit(rB, col0 + c, c + 32 <= NT ? 4 : 2);
-                    c = c2;
+                if (NSETS == 1) {
+                    uint32_t rA[32], rB[32];
+                    if (c < NTv) load(tbase, c, NT, rA);
+                    while (c < NTv) {
+                        tmem_wait_ld();
+                        int c2 = c + kStride;
+                        if (c2 < NTv) load(tbase, c2, NT, rB); else release();
+                        emit(rA, col0 + c, c + 32 <= NT ? 4 : 2);
+                        c = c2;
+                        if (c >= NTv) break;
+                        tmem_wait_ld();
+                        c2 = c + kStride;
+                        if (c2 < NTv) load(tbase, c2, NT, rA); else release();
+                        emit(rB, col0 + c, c + 32 <= NT ? 4 : 2);
+                        c = c2;
+                    }
+                } else {  // two warp sets overlap each other's loads and arithmetic: one register buffer per warp is enough
+                    uint32_t r[32];
+                    for (; c < NTv; c += kStride) {
+                        load(tbase, c, NT, r);
+                        tmem_wait_ld();
+                        if (c + kStride >= NTv) release();
+                        emit(r, col0 + c, c + 32 <= NT ? 4 : 2);
+                    }
                 }
                 if (!released) release();
                 if (warp == 4 && lane == 0) PAIR_TRACE(3, im, j, 1);
@@ -447,6 +479,10 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
     if (a.K % 16 || a.K / 2 + 2 * nt_max > 512)
         throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: A tile + two accumulators exceed the 512 TMEM columns");
+    // The epilogue drains accumulators at ~50 B/clk/SM (tcgen05.ld, tools/tmemld_bw.cu) and a K = 400 layer produces
+    // 41 B/clk/SM of them at the full tensor rate: with two buffers every hand-over latency is exposed, a third
+    // decouples the two pipelines.
+    pl.n_acc = a.K / 2 + 3 * nt_max <= 512 ? 3 : 2;
     pl.nk_total = a.K / 16;
     pl.ks = pair_slab_ksteps(a.K);
     pl.n_slabs = (pl.nk_total + pl.ks - 1) / pl.ks;
@@ -456,18 +492,16 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     const int tr_bytes = a.out_mode == 1 ? 8 * 32 * 33 * 4 : 0;
     static_assert(sizeof(PairShared) <= 1024, "barrier block");
     const int fixed = ((a.Nc * 4 + 15) / 16) * 16 + tr_bytes + 1024 + 16;
-    // A staging: a whole tile's slabs when that leaves the weight ring enough stages (timeline: with a buffer fewer the
-    // last slab's load starts only when the first buffer has been restaged and lands ~1 000 cycles late).
-    // Ring length: two issuers skip each other's stages and a parity wait can only tell "this fill" from "the fill
-    // before", so the fill before the one an issuer polls must be older than a stage that issuer has already consumed:
-    // n_stages >= n_slabs + 1 (one more for slack), and at least six for the L2 latency.
-    const int min_stages = pl.n_slabs + 2 > 6 ? pl.n_slabs + 2 : 6;
+    // A staging: a whole tile's slabs when that leaves the weight ring six stages.  Timeline: with a buffer fewer the last slab's load starts only when the first
+    // buffer has been restaged and lands ~1 000 cycles late; with a ring that holds less than two N-tiles the producer
+    // waits for MMA completions and the L2 latency is exposed.
+    const int min_stages = 6;
     pl.n_abuf = pl.n_slabs < kMaxABuf ? pl.n_slabs : kMaxABuf;
     while (pl.n_abuf > 2 && (kSmemTotal - pl.n_abuf * pl.a_slab_bytes - fixed) / pl.stage_bytes < min_stages) --pl.n_abuf;
     pl.b_off = pl.n_abuf * pl.a_slab_bytes;
     pl.n_stages = (kSmemTotal - pl.b_off - fixed) / pl.stage_bytes;
     if (pl.n_stages > kMaxStages) pl.n_stages = kMaxStages;
-    if (pl.n_stages < pl.n_slabs + 2 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: layer does not fit the shared-memory plan");
+    if (pl.n_stages < pl.n_slabs + 1 || pl.n_slabs > kMaxSlabs) throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: layer does not fit the shared-memory plan");
     pl.bias_off = pl.b_off + pl.n_stages * pl.stage_bytes;
     pl.tr_off = pl.bias_off + ((a.Nc * 4 + 15) / 16) * 16;
     pl.sh_off = (pl.tr_off + tr_bytes + 15) & ~15;
@@ -477,8 +511,8 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     if (a.out_mode == 1) {
         if (a.act != 2) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: the gains output applies the sigmoid");
         launch_pair_variant<2, 1, 2>(a, pl, maps, grid, s);
-    } else if (a.act == 0) launch_pair_variant<0, 0, 1>(a, pl, maps, grid, s);
-    else if (a.act == 1) launch_pair_variant<1, 0, 1>(a, pl, maps, grid, s);
+    } else if (a.act == 0) launch_pair_variant<0, 0, 2>(a, pl, maps, grid, s);
+    else if (a.act == 1) launch_pair_variant<1, 0, 2>(a, pl, maps, grid, s);
     else throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: unsupported activation/output combination");
     FVAD_LAUNCHED();
     FVAD_CUDA_CHECK(cudaGetLastError());
