@@ -178,6 +178,34 @@ public:
             gRbn_[l].ensure((size_t)H);
             FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
         }
+        // fc1 folded into the first GRU's input projection.  When the graph has no activation between them (fc1_relu == 0:
+        // the NSNet2 baseline), W1 (fc1 x + b1) + b = (W1 fc1) x + (W1 b1 + b): one K = 161 contraction instead of 161 -> 400
+        // followed by 400 -> 1200, the same function with 333 000 fewer multiply-adds per frame-step (12 % of the network) and
+        // one fp16 rounding of the activations less.  The product is formed in f64 and rounded to fp16 once.
+        // FVAD_NN_FOLD_FC1=0 keeps the two layers apart (A/B; what the f32 backend and the oracle always do).
+        fold_fc1_ = !w.fc1_relu;
+        if (const char *e = getenv("FVAD_NN_FOLD_FC1")) fold_fc1_ = fold_fc1_ && atoi(e) != 0;
+        if (fold_fc1_) {
+            const int NB = 161;
+            std::vector<float> Wf((size_t)3 * H * NB), bf((size_t)3 * H);
+            for (int o = 0; o < 3 * H; ++o) {
+                const float *wr = w.gru_W[0].data() + (size_t)o * H;
+                double acc_b = (double)w.gru_Wb[0][(size_t)o] + (o < 2 * H ? (double)w.gru_Rb[0][(size_t)o] : 0.0);
+                for (int k = 0; k < H; ++k) acc_b += (double)wr[k] * (double)w.fc1_b[(size_t)k];
+                bf[(size_t)o] = (float)acc_b;
+                for (int i = 0; i < NB; ++i) {
+                    double acc = 0.0;
+                    for (int k = 0; k < H; ++k) acc += (double)wr[k] * (double)w.fc1_w[(size_t)k * NB + i];
+                    Wf[(size_t)o * NB + i] = (float)acc;
+                }
+            }
+            gp = (pmask & 2) != 0;
+            // K = 176: the A tile takes 88 TMEM columns, which leaves room for three accumulators of 128 (the layer is
+            // accumulator-drain bound: 1 200 fp32 columns to read back per 176-deep contraction)
+            build_layer(gWf_, Wf.data(), bf.data(), perm.data(), 3 * H, NB, 176,
+                        gp ? T{48, 128, 128, 128, 128, 128, 128, 128, 128, 128} : T{144, 144, 144, 144, 144, 144, 144, 144, 48}, gp);
+            gWf_.a_tmem = ts ? 1 : 0;
+        }
         gp = (pmask & 4) != 0;
         build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, gp ? T{112, 112, 128, 128, 128} : T{208, 208, 192}, gp);
         gp = (pmask & 8) != 0;
@@ -199,7 +227,7 @@ public:
         const int QB = std::min(q_total, 2 * n_sm_);  // tiles per sub-batch
         if (!sp.feat16) throw Error(FVAD_ERR_INVALID_ARGUMENT, "the tensor-core backend reads the fp16 feature rows");
         a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
-        x1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
+        if (!fold_fc1_) x1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
         xp_.ensure((size_t)QB * kSteps * tc::tile_bytes(1200) / 2);
         h1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
         h2_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
@@ -212,9 +240,10 @@ public:
             mark(0, s);
             tc::launch_tc_pack(pa, s);
             mark(1, s);
-            gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
+            if (!fold_fc1_) gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
             mark(2, s);
-            gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
+            if (fold_fc1_) gemm(gWf_, a0, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
+            else gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             mark(3, s);
             gru(0, h1_.p, Q, 0, s);
             mark(4, s);
@@ -262,7 +291,8 @@ public:
 
 private:
     int n_sm_ = 148, fc1_relu_ = 0;
-    Layer fc1_, gW_[2], fc2_, fc3_, fc4_;
+    Layer fc1_, gW_[2], gWf_, fc2_, fc3_, fc4_;
+    bool fold_fc1_ = false;   // fc1 folded into W1 (gWf_): see the constructor
     DevBuf<__half> gR_[2], gR2_[2];
     // per-layer CUDA-event timing (events only, no extra synchronisation); FVAD_NN_TIMING=1 prints the lifetime sums
     bool timing_ = false;
@@ -324,7 +354,7 @@ private:
         const char *tp = getenv("FVAD_GEMM_TRACE");
         if (!tp || gtraced_) return;
         const char *want = getenv("FVAD_GEMM_TRACE_LAYER");
-        const Layer *sel = &gW_[0];
+        const Layer *sel = fold_fc1_ ? &gWf_ : &gW_[0];
         if (want) sel = !strcmp(want, "fc1") ? &fc1_ : !strcmp(want, "W2") ? &gW_[1] : !strcmp(want, "fc2") ? &fc2_ : !strcmp(want, "fc3") ? &fc3_ : &gW_[0];
         if (sel != &L) return;
         gtraced_ = true;
