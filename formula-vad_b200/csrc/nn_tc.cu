@@ -175,6 +175,7 @@ public:
             }
             gR2_[l].ensure(img2.size());
             FVAD_CUDA_CHECK(cudaMemcpy(gR2_[l].p, img2.data(), img2.size() * sizeof(__half), cudaMemcpyHostToDevice));
+            tc::build_gru_pair_map(gRmap_[l], gR2_[l].p);
             gRbn_[l].ensure((size_t)H);
             FVAD_CUDA_CHECK(cudaMemcpy(gRbn_[l].p, w.gru_Rb[l].data() + 2 * H, H * sizeof(float), cudaMemcpyHostToDevice));
         }
@@ -294,6 +295,7 @@ private:
     Layer fc1_, gW_[2], gWf_, fc2_, fc3_, fc4_;
     bool fold_fc1_ = false;   // fc1 folded into W1 (gWf_): see the constructor
     DevBuf<__half> gR_[2], gR2_[2];
+    CUtensorMap gRmap_[2];  // TMA view of gR2_ (pair kernel)
     // per-layer CUDA-event timing (events only, no extra synchronisation); FVAD_NN_TIMING=1 prints the lifetime sums
     bool timing_ = false;
     std::vector<cudaEvent_t> tev_;   // 10 per sub-batch of the current push
@@ -315,7 +317,7 @@ private:
         unsigned long long *tr = nullptr;
         const char *tp = getenv("FVAD_GRU_TRACE");
         if (tp && l == 0 && !traced_) { trace_.ensure(54 * 25 * 8); FVAD_CUDA_CHECK(cudaMemsetAsync(trace_.p, 0, 54 * 25 * 8 * 8, s)); tr = trace_.p; }
-        if (pair_) tc::launch_tc_gru2(tc::GruArgs{xp_.p, gR2_[l].p, gRbn_[l].p, hout, Q, t_store_min, nullptr}, n_sm_, s);
+        if (pair_) tc::launch_tc_gru2(tc::GruArgs{xp_.p, gR2_[l].p, gRbn_[l].p, hout, Q, t_store_min, tr}, gRmap_[l], n_sm_, s);
         else tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[l].p, gRbn_[l].p, hout, Q, t_store_min, tr}, n_sm_, s);
         if (tr) {  // debug only: dump CTA 0's timeline of the first GRU launch
             traced_ = true;

@@ -50,6 +50,8 @@ void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s);
 struct PairMaps {
     CUtensorMap m[2 * kMaxNTiles];
 };
+void encode_tiled_map(CUtensorMap *m, CUtensorMapDataType dt, unsigned rank, void *base, const cuuint64_t *gdim, const cuuint64_t *gstr,
+                      const cuuint32_t *box);
 int pair_slab_ksteps(int K);
 void build_pair_maps(PairMaps &maps, const void *img2, int K, int n_tiles, const int *nt_size, const unsigned *nt_off);
 void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStream_t s);
@@ -69,8 +71,10 @@ struct GruArgs {
     unsigned long long *trace;  // debug (FVAD_GRU_TRACE): CTA 0 logs clock64 at [step][chunk][event], nullptr otherwise
 };
 void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
-// CTA-pair version (nn_tc_gru2.cu): Rimg is the split image (per chunk two 24-row halves tiled with R = 24)
-void launch_tc_gru2(const GruArgs &a, int n_sm, cudaStream_t s);
+// CTA-pair version (nn_tc_gru2.cu): Rimg is the split image (per chunk two 24-row halves tiled with R = 24), fetched by TMA
+// through `rmap` (build_gru_pair_map)
+void build_gru_pair_map(CUtensorMap &rmap, const void *Rimg2);
+void launch_tc_gru2(const GruArgs &a, const CUtensorMap &rmap, int n_sm, cudaStream_t s);
 
 // feature rows fp16 [SC][4+50K][176] -> fp16 tiles [q][54] of 176 columns for sequences seq0 .. seq0+128*Q-1
 struct PackArgs {

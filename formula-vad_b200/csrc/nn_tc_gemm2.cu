@@ -435,6 +435,15 @@ EncodeTiledFn encode_tiled() {
 
 }  // namespace
 
+// cuTensorMapEncodeTiled with the settings every map of this backend uses (no interleave, no swizzle, zero fill)
+void encode_tiled_map(CUtensorMap *m, CUtensorMapDataType dt, unsigned rank, void *base, const cuuint64_t *gdim, const cuuint64_t *gstr,
+                      const cuuint32_t *box) {
+    const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    const CUresult rc = encode_tiled()(m, dt, rank, base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) throw Error(FVAD_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)rc) + ")");
+}
+
 // K-steps per weight slab of the pair kernel: equal pieces of at most 8 K-steps (the issue loop's unroll)
 int pair_slab_ksteps(int K) {
     const int nk = K / 16;
@@ -454,11 +463,7 @@ void build_pair_maps(PairMaps &maps, const void *img2, int K, int n_tiles, const
             const cuuint64_t gdim[2] = {(cuuint64_t)NH * 2, (cuuint64_t)K / 8};  // 8-byte elements: a core column is NH*16 bytes
             const cuuint64_t gstr[1] = {(cuuint64_t)NH * 16};
             const cuuint32_t box[2] = {(cuuint32_t)NH * 2, (cuuint32_t)(2 * ks)};
-            const cuuint32_t estr[2] = {1, 1};
-            const CUresult rc = encode_tiled()(&maps.m[2 * j + r], CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, base, gdim, gstr, box, estr,
-                                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            if (rc != CUDA_SUCCESS) throw Error(FVAD_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)rc) + ")");
+            encode_tiled_map(&maps.m[2 * j + r], CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, base, gdim, gstr, box);
         }
 }
 

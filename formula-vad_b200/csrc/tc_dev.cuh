@@ -135,6 +135,14 @@ __device__ __forceinline__ void tma2_load_2d(void *dst_smem, const void *tmap, u
         : "memory");
 }
 
+__device__ __forceinline__ void tma2_load_3d(void *dst_smem, const void *tmap, uint32_t bar_cluster_addr, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(tmap), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05
 template <uint32_t NCOLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t *slot_in_smem) {  // whole warp

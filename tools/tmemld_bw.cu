@@ -45,7 +45,8 @@ __global__ void __launch_bounds__(128, 1) shape_kernel(int reps, unsigned long l
         if (SHAPE == 1) { ld_16x128b_x16(t, a); ld_16x128b_x16(t + (16u << 16), b); }      // 2 x (16 lanes x 64 columns) = 8 KB
         if (SHAPE == 2) { tmem_ld32(t, a); tmem_ld32(t + 32, b); }                          // 2 x (32 lanes x 32 columns) = 8 KB
         tmem_wait_ld();
-        sink += a[r & 31] + b[r & 31];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sink ^= a[i] ^ b[i];
     }
     const long long t1 = clock64();
     if ((threadIdx.x & 31) == 0) out[blockIdx.x * 16 + warp] = (unsigned long long)(t1 - t0);
@@ -94,7 +95,9 @@ __global__ void __launch_bounds__(32 * (LDW + 1), 1) ld_kernel(int reps, unsigne
             for (int d = 0; d < DEPTH; ++d) tmem_ld32(t + 32 * (d & 3), v[d]);
             tmem_wait_ld();
 #pragma unroll
-            for (int d = 0; d < DEPTH; ++d) sink += v[d][r & 31];
+            for (int d = 0; d < DEPTH; ++d)
+#pragma unroll
+                for (int i = 0; i < 32; ++i) sink ^= v[d][i];
         }
         const long long t1 = clock64();
         if ((threadIdx.x & 31) == 0) out[blockIdx.x * 16 + warp] = (unsigned long long)(t1 - t0);
