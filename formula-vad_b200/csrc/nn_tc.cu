@@ -309,7 +309,7 @@ private:
     DevBuf<unsigned long long> trace_, gtrace_;
     bool gtraced_ = false;
     bool traced_ = false;
-    bool pair_ = false;
+    bool pair_ = true;        // GRU on CTA pairs (nn_tc_gru2.cu); FVAD_GRU_PAIR=0: the one-CTA kernel (A/B)
     bool gemm_ts_ = true;     // A tile in TMEM (FVAD_GEMM_TS=0: resident in shared memory, the first design)
     bool gemm_pair_ = true;   // CTA-pair GEMM (nn_tc_gemm2.cu) for W1/W2/fc2/fc3/fc4; FVAD_GEMM_PAIR=0: every layer on the one-CTA kernel (A/B)
 

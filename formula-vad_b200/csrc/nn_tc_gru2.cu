@@ -3,26 +3,31 @@
 // Replaces the ONNX GRU nodes inside `onnx_instance.run()` (reference src/NSNet2.zig:220; ONNX GRU semantics with
 // linear_before_reset = 1, gate order z,r,h -- SURVEY App. C); same math and data layout as nn_tc_gru.cu.
 //
-// What bounds a GRU step of 128 sequences on one SM (measured, tools/tmemld_bw.cu and the step timelines): 25 chunks x
-// 25 MMAs of 128x48x16 = 15 000 tensor cycles, against (a) 0.96 MB of recurrent weights through L2 -> shared memory
-// (64 B/clk/SM at that rate; the L2 delivers ~43 with every SM pulling) and (b) 25 x (48 accumulator + 8 hidden-state)
-// columns x 128 lanes x 4 B = 717 KB through tcgen05.ld, which moves 48.5 B/clk/SM: 14 800 cycles.  Three pipes loaded
-// to 100 % each cannot overlap perfectly; the one-CTA kernel runs at ~21 000 cycles per step.  This kernel takes load
-// off (a) and (b):
+// What bounds a GRU step of 128 sequences on one SM (step timelines, FVAD_GRU_TRACE; tools/mmabw_pair.cu,
+// tools/tmemld_bw.cu): 25 chunks x 25 MMAs of 128x48x16 = 15 000 tensor cycles.  Neither the tensor pipe (pair MMAs
+// run at N/2 cycles for every N) nor the accumulator drain (tcgen05.ld: 200 B/clk/SM with four warps) is the limit;
+// the SM's L1 / shared-memory array is (128 B/clk): per chunk it takes the weight fill, the tensor cores' reads of
+// it, the epilogue's x-projection loads (12 KB) and its h_t stores (8 KB).  One CTA: 64 + 64 + 33 = 161 B/clk at the
+// tensor rate -> >= 19 000 cycles per step, ~21 000 measured.  This kernel:
 //   * CTA pair: one 256-row MMA per K-step; each CTA keeps its own 128 sequences' hidden state and accumulators in its
-//     own TMEM and only HALF of each R chunk (24 of the 48 gate rows) in its shared memory -- the weight stream per SM
-//     halves.  Each half is a TMA tile load (.cta_group::2) whose bytes complete on the LEADER's barrier (no relay);
-//     every barrier operation uses default CTA-scope semantics (tc_dev.cuh: mbar_arrive_addr);
-//   * the shared memory the half-size ring frees (5 x 19 KB instead of 5 x 38 KB) holds h_{t-1} as fp16 in a
-//     thread-private layout: the epilogue thread that wrote h_t[row][chunk] is the one that needs it for
-//     h_{t+1} = n + z (h_t - n), so the blend operand comes from shared memory instead of a tcgen05.ld (-12 % drain);
-//   * h-ready is signalled per GROUP OF 5 CHUNKS: K-step kk of step t+1 reads exactly the 16 hidden units chunk kk of
-//     step t produced, so the issuers start step t+1 while the last epilogues of step t are still running;
-//   * two MMA-issuing threads (even / odd chunks, one accumulator each) as in the one-CTA kernel.
+//     own TMEM and only HALF of each R chunk (24 of the 48 gate rows) in its shared memory: fill 32 + reads 64 (own
+//     tensor core + the peer's) B/clk.  Each half is a TMA tile load (.cta_group::2) whose bytes complete on the
+//     LEADER's barrier (no relay); every barrier operation uses default CTA-scope semantics (tc_dev.cuh:
+//     mbar_arrive_addr);
+//   * the hidden state is SINGLE-buffered in TMEM (200 columns), which leaves room for SIX accumulators: the issuers
+//     run up to six chunks ahead of the epilogue and the pipe never waits for a drain inside a step.  The epilogue
+//     parks h_t in shared memory (fp16, thread-private layout -- the half-size ring frees the space) while the step's
+//     MMAs still read h_{t-1} (which the blend h_t = n + z (h_{t-1} - n) also takes from TMEM); once the step's last
+//     MMAs have retired each epilogue thread copies its chunks of h_t into TMEM for the next step;
+//   * two MMA-issuing threads (even / odd chunks) as in the one-CTA kernel.
+// Measured: ~20 500-21 400 cycles per step at a lower power draw (the step runs at the board's power cap, so the
+// saved energy comes back as clock): 4 % faster than one CTA per 20 stream-hours.  The array is still the limit
+// (96 + 46 B/clk); what would lift it is fusing the input projection into this kernel (no x-projection round trip),
+// which needs TMEM for a second A operand.
 //
 // Roles (384 threads per CTA): warp 0 R producer (TMA), warps 1 and 3 MMA issuers (leader only; commits multicast to
 // both CTAs), warp 2 TMEM allocator, warps 4..7 / 8..11 epilogue of the even / odd chunks (this CTA's 128 rows).
-// TMEM columns: h ping [0,200) | h pong [200,400) | acc0 [400,448) | acc1 [448,496).
+// TMEM columns: h [0,200) | accumulator a at [200 + 48a, 248 + 48a), a = (54-step chunk counter) % 6.
 #include "nn_tc.cuh"
 #include "tc_dev.cuh"
 
@@ -41,7 +46,8 @@ constexpr int kStages = 5;
 constexpr int kGru2Threads = 384;                   // 4 control warps + 2 x 4 epilogue warps
 constexpr int kHsBytes = kChunks * kTileM * 32;     // h_{t-1} as fp16, [chunk][row][16 units]: 102 400
 constexpr int kGru2Smem = kStages * kHalfBytes + kHsBytes + kH * 4 + 1024;
-constexpr uint32_t kColH0 = 0, kColH1 = 200, kColAcc0 = 400, kColAcc1 = 448;
+constexpr int kAccs = 6;                            // accumulators of 48 columns next to the 200 columns of h
+constexpr uint32_t kColH = 0, kColAcc = 200;
 
 // timeline probe: event e of (step t, chunk c) of the first tile pair of CTA 0 (the leader): 0 issuer acc_empty ok, 1 full ok,
 // 2 issued + committed, 3 epilogue acc_full ok, 4 accumulator in registers, 5 chunk done (h signalled), 6 issuer starts chunk 0
@@ -50,9 +56,10 @@ constexpr uint32_t kColH0 = 0, kColH1 = 200, kColAcc0 = 400, kColAcc1 = 448;
 struct Gru2Shared {
     uint64_t full[kStages];       // LEADER's: both CTAs' halves of an R chunk complete their bytes here
     uint64_t empty[kStages];      // per CTA: the MMAs over this stage are done (multicast commit)
-    uint64_t acc_full[2];         // per CTA (multicast commit)
-    uint64_t acc_empty[2];        // LEADER's: 4 epilogue warps of the group in each CTA
-    uint64_t h_rdy[kChunks / 5];  // LEADER's: the hidden units of chunks 5g..5g+4 of the step are in both CTAs' TMEM (5 x (4 + 4) warps)
+    uint64_t acc_full[kAccs];     // per CTA (multicast commit)
+    uint64_t acc_empty[kAccs];    // LEADER's: 4 epilogue warps of the chunk's group in each CTA
+    uint64_t step_done;           // per CTA (multicast commit by each issuer after its last chunk of a step): h may be overwritten
+    uint64_t h_ready;             // LEADER's: h_t is in both CTAs' TMEM (8 + 8 epilogue warps)
     uint32_t tmem_base;
     uint32_t passed[2];           // LEADER's: per MMA issuer, 1 + the last chunk (producer's sequence) whose full-wait it has passed
 };
@@ -85,11 +92,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
             mbar_init(&sh->full[i], 1);
             mbar_init(&sh->empty[i], 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kAccs; ++i) {
             mbar_init(&sh->acc_full[i], 1);
             mbar_init(&sh->acc_empty[i], 8);   // 4 epilogue warps of the group in each CTA
         }
-        for (int i = 0; i < kChunks / 5; ++i) mbar_init(&sh->h_rdy[i], 40);
+        mbar_init(&sh->step_done, 2);
+        mbar_init(&sh->h_ready, 16);
         sh->passed[0] = sh->passed[1] = 0;
         fence_mbar_init();
     }
@@ -132,18 +140,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
         if (leader && elect_one()) {
             constexpr uint32_t idesc = make_idesc_f16(2 * kTileM, kChunkRows);
             const uint32_t me = warp == 1 ? 0u : 1u;
-            const uint32_t d = tmem + (me ? kColAcc1 : kColAcc0);
+            const uint32_t hold = tmem + kColH;
             volatile uint32_t *passed_me = &sh->passed[me], *passed_other = &sh->passed[me ^ 1u];
-            uint32_t step = 0, use = 0;
+            uint32_t step = 0;
             for (int ip = 0; ip < n_p; ++ip)
                 for (int t = 0; t < kSteps; ++t, ++step) {
-                    const uint32_t hold = tmem + ((t & 1) ? kColH1 : kColH0);
                     for (int c = (int)me; c < kChunks; c += 2) {
                         const uint32_t it = step * kChunks + (uint32_t)c;
                         const uint32_t st = it % kStages, ph = (it / kStages) & 1;
+                        const uint32_t acc = it % kAccs, use = it / kAccs;
+                        const uint32_t d = tmem + kColAcc + acc * kChunkRows;
                         if (c == 0) GRU2_TRACE(6, t, 0);
-                        // the weights first (they land long before), then the accumulator: the path drained -> first MMA is
-                        // the critical one of the two-accumulator ring
                         if (it >= (uint32_t)kStages && (((it - kStages) % kChunks) & 1u) != me) {
                             while (*passed_other <= it - kStages) {}
                             __threadfence_block();
@@ -154,34 +161,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                         GRU2_TRACE(1, t, c);
                         const uint64_t bd0 = make_smem_desc(smem_u32(smem + st * kHalfBytes), kHalfRows * 16, 128);
                         const uint32_t blo = (uint32_t)bd0, bhi = (uint32_t)(bd0 >> 32);
-                        mbar_wait(&sh->acc_empty[me], (use & 1) ^ 1);
-                        ++use;
+                        mbar_wait(&sh->acc_empty[acc], (use & 1) ^ 1);
+                        if (c < 2) mbar_wait(&sh->h_ready, step & 1);  // h_{t-1} (or the zero fill) is in both CTAs' TMEM
                         tc_fence_after();
                         GRU2_TRACE(0, t, c);
                         // K-step kk: h columns [8kk, 8kk+8); R slab 2 core columns = 2*24*16 B = 48 descriptor units on
-                        if (c < 2) {
-                            // this thread's first chunk of the step: K-step kk needs the 16 hidden units that chunk kk of the
-                            // previous step (or the zero fill) produced, in both CTAs; readiness comes in groups of 5 chunks
+                        mma2_ts_lohi<false>(d, hold, blo, bhi, idesc);
 #pragma unroll
-                            for (int grp = 0; grp < kChunks / 5; ++grp) {
-                                mbar_wait(&sh->h_rdy[grp], step & 1);
-                                tc_fence_after();
-#pragma unroll
-                                for (int kk = 5 * grp; kk < 5 * grp + 5; ++kk) {
-                                    if (kk == 0) mma2_ts_lohi<false>(d, hold, blo, bhi, idesc);
-                                    else mma2_ts_lohi<true>(d, hold + kk * 8, blo + kk * (2 * kHalfRows), bhi, idesc);
-                                }
-                            }
-                        } else {
-                            mma2_ts_lohi<false>(d, hold, blo, bhi, idesc);
-#pragma unroll
-                            for (int kk = 1; kk < kH / 16; ++kk)
-                                mma2_ts_lohi<true>(d, hold + kk * 8, blo + kk * (2 * kHalfRows), bhi, idesc);
-                        }
+                        for (int kk = 1; kk < kH / 16; ++kk)
+                            mma2_ts_lohi<true>(d, hold + kk * 8, blo + kk * (2 * kHalfRows), bhi, idesc);
                         mma2_commit_mc(&sh->empty[st], 3);
-                        mma2_commit_mc(&sh->acc_full[me], 3);
+                        mma2_commit_mc(&sh->acc_full[acc], 3);
                         GRU2_TRACE(2, t, c);
                     }
+                    mma2_commit_mc(&sh->step_done, 3);  // every MMA of this thread that reads h_{t-1} has retired when this lands
                 }
         }
     } else if (warp >= 4) {
@@ -190,31 +183,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
         const int wq = warp & 3;
         const int row = wq * 32 + lane;
         const uint32_t lane_off = (uint32_t)(wq * 32) << 16;
-        const uint32_t acc = tmem + lane_off + (g ? kColAcc1 : kColAcc0);
         const size_t row_off = (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16;
-        const uint32_t acc_empty_leader = mapa_u32(&sh->acc_empty[g], 0);
-        const uint32_t h_rdy_leader = mapa_u32(&sh->h_rdy[0], 0);
+        const uint32_t acc_empty_leader = mapa_u32(&sh->acc_empty[0], 0);
+        const uint32_t h_ready_leader = mapa_u32(&sh->h_ready, 0);
+        const uint32_t th = tmem + lane_off + kColH;
         uint4 *hrow = reinterpret_cast<uint4 *>(hs + (size_t)row * 32);  // + chunk * (kTileM * 32) bytes
-        uint32_t use = 0;
+        uint32_t step = 0;
         for (int ip = 0; ip < n_p; ++ip) {
             const int q = 2 * (pair0 + ip * n_pair_ctas) + (int)rank;
             const bool valid = q < a.Q;  // an odd tile count leaves the last pair's second tile as padding
-            // h_{-1} = 0: zero this group's columns of the ping buffer and of the shared-memory copy
+            // h_{-1} = 0: zero this group's chunks of h in TMEM (the previous tile's last MMAs have retired: the step_done
+            // wait below)
             {
                 uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 for (int c = g; c < kChunks; c += 2) {
-                    tmem_st8(tmem + lane_off + kColH0 + c * 8, z);
-                    hrow[c * (kTileM * 2)] = make_uint4(0, 0, 0, 0);
-                    hrow[c * (kTileM * 2) + 1] = make_uint4(0, 0, 0, 0);
+                    tmem_st8(th + c * 8, z);
                 }
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0)
-                    for (int c = g; c < kChunks; c += 2) mbar_arrive_addr(h_rdy_leader + 8u * (uint32_t)(c / 5));
+                if (lane == 0) mbar_arrive_addr(h_ready_leader);
             }
-            for (int t = 0; t < kSteps; ++t) {
-                const uint32_t hnew = tmem + lane_off + ((t & 1) ? kColH0 : kColH1);
+            for (int t = 0; t < kSteps; ++t, ++step) {
                 const uint8_t *xpt = reinterpret_cast<const uint8_t *>(a.xp) + (size_t)(q * kSteps + t) * tile_bytes(3 * kH) + row_off;
                 uint8_t *hot = reinterpret_cast<uint8_t *>(a.hout) + (size_t)(q * kSteps + t) * tile_bytes(kH) + row_off;
                 const bool store = valid && t >= a.t_store_min;
@@ -231,29 +221,38 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                         for (int i = 0; i < 6; ++i)
                             xn[i] = __ldg(reinterpret_cast<const uint4 *>(xpt + (size_t)((c + 2) * 6 + i) * (kTileM * 16)));
                     }
-                    const uint4 ho0 = hrow[c * (kTileM * 2)], ho1 = hrow[c * (kTileM * 2) + 1];  // h_{t-1} of this row's 16 units
-                    mbar_wait(&sh->acc_full[g], use & 1);
-                    ++use;
+                    const uint32_t it = step * kChunks + (uint32_t)c;
+                    const uint32_t ai = it % kAccs, use = it / kAccs;
+                    const uint32_t acc = tmem + lane_off + kColAcc + ai * kChunkRows;
+                    mbar_wait(&sh->acc_full[ai], use & 1);
                     tc_fence_after();
                     if (wq == 0 && lane == 0) GRU2_TRACE(3, t, c);
-                    uint32_t az[16], ar[16], an[16];
+                    uint32_t az[16], ar[16], an[16], ho[8];
                     tmem_ld16(acc, az);
                     tmem_ld16(acc + 16, ar);
                     tmem_ld16(acc + 32, an);
+                    tmem_ld8(th + c * 8, ho);  // h_{t-1} of this row's 16 units: TMEM keeps it untouched for the whole step
                     tmem_wait_ld();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive_addr(acc_empty_leader);  // drained: the pair's next chunk may overwrite it
+                    if (lane == 0) mbar_arrive_addr(acc_empty_leader + 8u * ai);  // drained: a later chunk may overwrite it
                     if (wq == 0 && lane == 0) GRU2_TRACE(4, t, c);
 
                     const uint32_t *xw = reinterpret_cast<const uint32_t *>(x);  // 24 words: z[0..7] r[8..15] n[16..23] (pairs)
-                    const uint32_t ho[8] = {ho0.x, ho0.y, ho0.z, ho0.w, ho1.x, ho1.y, ho1.z, ho1.w};
+                    // Rb of the n gate for the chunk's 16 units: four broadcast 16-byte loads (the L1 / shared-memory pipe is the
+                    // loaded resource of this kernel: weights in and out, the x projections and h_t all go through it)
+                    float rb[16];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 v = *reinterpret_cast<const float4 *>(rbn_s + c * kChunkUnits + 4 * i);
+                        rb[4 * i] = v.x; rb[4 * i + 1] = v.y; rb[4 * i + 2] = v.z; rb[4 * i + 3] = v.w;
+                    }
                     uint32_t hn[8];
 #pragma unroll
                     for (int p = 0; p < 8; ++p) {
                         const float2 xz = unpack_h2(xw[p]), xr = unpack_h2(xw[8 + p]), xnn = unpack_h2(xw[16 + p]);
                         const float2 hp = unpack_h2(ho[p]);
-                        const float b0 = rbn_s[c * kChunkUnits + 2 * p], b1 = rbn_s[c * kChunkUnits + 2 * p + 1];
+                        const float b0 = rb[2 * p], b1 = rb[2 * p + 1];
                         const float z0 = sigmoid_fast(xz.x + __uint_as_float(az[2 * p]));
                         const float z1 = sigmoid_fast(xz.y + __uint_as_float(az[2 * p + 1]));
                         const float r0 = sigmoid_fast(xr.x + __uint_as_float(ar[2 * p]));
@@ -264,7 +263,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                         const float h1 = n1 + z1 * (hp.y - n1);
                         hn[p] = pack_h2(h0, h1);
                     }
-                    tmem_st8(hnew + c * 8, hn);
                     hrow[c * (kTileM * 2)] = make_uint4(hn[0], hn[1], hn[2], hn[3]);
                     hrow[c * (kTileM * 2) + 1] = make_uint4(hn[4], hn[5], hn[6], hn[7]);
                     if (store) {
@@ -272,13 +270,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                         *reinterpret_cast<uint4 *>(p) = make_uint4(hn[0], hn[1], hn[2], hn[3]);
                         *reinterpret_cast<uint4 *>(p + kTileM * 16) = make_uint4(hn[4], hn[5], hn[6], hn[7]);
                     }
-                    if (t < kSteps - 1) {  // h_t[16c..16c+15] of this warp's rows is in TMEM: K-step c of the next step may read it
-                        tmem_wait_st();    // (the next pair's zero fill arrives for its own t = 0)
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive_addr(h_rdy_leader + 8u * (uint32_t)(c / 5));
-                    }
                     if (wq == 0 && lane == 0) GRU2_TRACE(5, t, c);
+                }
+                // The step's last MMAs (both issuers) have read h_{t-1}: its TMEM columns may now take h_t, which this
+                // thread holds in shared memory for the chunks it computed.  (After the tile's last step the next tile's
+                // zero fill follows instead.)
+                mbar_wait(&sh->step_done, step & 1);
+                tc_fence_after();
+                if (t < kSteps - 1) {
+                    for (int c = g; c < kChunks; c += 2) {
+                        const uint4 v0 = hrow[c * (kTileM * 2)], v1 = hrow[c * (kTileM * 2) + 1];
+                        const uint32_t hv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+                        tmem_st8(th + c * 8, hv);
+                    }
+                    tmem_wait_st();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_addr(h_ready_leader);
                 }
             }
         }
