@@ -26,7 +26,9 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 
 # algorithmic work per unit.  Unit = one NSNet2 frame hop (10 ms of one channel).
-FLOP_PER_FRAME_STEP = 2 * 2_681_000          # fc1 + 2 x (GRU W + GRU R) + fc2 + fc3 + fc4, MAC x 2
+FLOP_PER_FRAME_STEP = 2 * 2_681_000          # fc1 + 2 x (GRU W + GRU R) + fc2 + fc3 + fc4, MAC x 2 (as the reference executes it)
+MAC_FC1, MAC_GRU_W, MAC_GRU_R, MAC_TAIL = 64_400, 480_000, 480_000, 240_000 + 360_000 + 96_600
+MAC_FOLDED_W1 = 161 * 1200                   # fc1 folded into the first GRU's input projection (nn_tc.cu): one K = 161 layer
 STEPS_PER_CHUNK, FRAMES_PER_CHUNK = 54, 50   # the reference evaluates 54 rows per 50 output frames
 ISTFT_BYTES_PER_FRAME = 161 * 8 + 161 * 4 + 160 * 4  # spectrum row + f32 gain row read, one hop of y16 written
 
@@ -46,28 +48,35 @@ def measured_peaks():
     return 6650.0, 1400.0, "fallback"  # B200_PROFILING.md fallback figures
 
 
+def _traffic_file(kernel: str):
+    """the newest committed `ncu --set full` capture (profiles/rNN_traffic.json, written by tools/ncu_traffic.py) that
+    holds `kernel`"""
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            with open(p) as f:
+                d = json.load(f)
+            if kernel in d.get("kernels", {}):
+                return d
+    return None
+
+
 def ncu_traffic(kernel: str, streams: int, hours: float, sample_rate: int):
     """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one launch of `kernel`, from the committed
-    `ncu --set full` capture of this same workload (profiles/r01_traffic.json, written by tools/ncu_traffic.py);
-    None when no capture of this workload is on file."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if not os.path.exists(p):
+    `ncu --set full` capture of this same workload; None when no capture of this workload is on file."""
+    d = _traffic_file(kernel)
+    if not d:
         return None
-    with open(p) as f:
-        d = json.load(f)
     w = d.get("workload", {})
     if (w.get("streams"), w.get("hours"), w.get("sample_rate")) != (streams, hours, sample_rate):
         return None
-    return d.get("kernels", {}).get(kernel, {}).get("dram_bytes_per_launch")
+    return d["kernels"][kernel].get("dram_bytes_per_launch")
 
 
 def ncu_traffic_chunks(kernel: str):
     """chunks per stream the captured launch covered (the first, full-size span of a step)"""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if not os.path.exists(p):
-        return None
-    with open(p) as f:
-        return json.load(f).get("kernels", {}).get(kernel, {}).get("chunks_per_stream")
+    d = _traffic_file(kernel)
+    return d["kernels"][kernel].get("chunks_per_stream") if d else None
 
 
 class ClockSampler:
@@ -251,6 +260,54 @@ def workload_config(args):
             "parallelism": f"stream-sharded x{args.gpus}, no collective"}
 
 
+def run_48k_stereo(fv, wd, nn_mode, local: int, seeds, streams: int, hours: float, steps: int):
+    """The reference-legal shape (VADPipeline.zig:55-58 accepts 48 kHz only; main.zig:135-142 runs 2 channels, i.e. two
+    NSNet2 sequences per stream-chunk): device-resident and host-f32 end-to-end realtime factor, audio seconds counted
+    per STREAM.  A short workload next to the headline one (synthetic; channel 1 = channel 0 mixed with a neighbour
+    stream, so speech is common to both channels and the noise is not)."""
+    import torch
+    sr, C = 48000, 2
+    x16, _ = fv.synth.onboard_batch_torch(seeds[:streams], hours * 3600.0, 16000, f"cuda:{local}")
+    nxt = torch.cat([x16[:, 1:], x16[:, -1:]], dim=1)
+    x = torch.empty((streams, C, x16.shape[1] * 3), dtype=torch.float32, device=x16.device)
+    x[:, 0, 0::3] = x16
+    x[:, 0, 1::3] = x16 + (nxt - x16) * (1.0 / 3.0)
+    x[:, 0, 2::3] = x16 + (nxt - x16) * (2.0 / 3.0)
+    x[:, 1] = 0.8 * x[:, 0] + 0.2 * torch.roll(x[:, 0], 1, dims=0)
+    del x16, nxt
+    n = x.shape[2]
+    n_chunks = n // 24000
+    audio_sec = streams * n_chunks * 24000 / sr
+    gp = fv.BatchPipeline(streams, sr, C, wd, nn_mode=nn_mode, device=local)
+    ptrs = [x[s, c].data_ptr() for s in range(streams) for c in range(C)]
+    for _ in range(3):
+        gp.push_pointers(ptrs, n, on_device=True)
+    torch.cuda.synchronize()
+    ms = 0.0
+    for _ in range(steps):
+        gp.push_pointers(ptrs, n, on_device=True)
+        ms += gp.stats()["last_push_device_ms"]
+    ms /= steps
+    xh = torch.empty(x.shape, dtype=torch.float32, pin_memory=True)
+    xh.copy_(x)
+    torch.cuda.synchronize()
+    hp = [xh[s, c].data_ptr() for s in range(streams) for c in range(C)]
+    gp.push_pointers(hp, n, on_device=False)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        gp.push_pointers(hp, n, on_device=False)
+        segs = [gp.segments(s) for s in range(streams)]
+    torch.cuda.synchronize()
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / steps
+    gp.close()
+    return {"workload": f"full pipeline, {streams} streams x {hours:g} h, 48000 Hz x {C} channels (the shape the reference accepts: "
+                        f"{streams * C} NSNet2 sequences per 0.5 s)", "value": audio_sec / (ms * 1e-3), "unit": "stream-audio-sec/sec",
+            "ms_per_step": ms, "steps": steps, "segments_found": int(sum(len(g) for g in segs)),
+            "e2e": {"value": audio_sec / (e2e_ms * 1e-3), "unit": "stream-audio-sec/sec", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(streams * C * n * 4), "input": "pinned host f32 planar, double-buffered H2D"}}
+
+
 def run_native(args):
     import torch
     import torch.distributed as dist
@@ -386,7 +443,13 @@ def run_native(args):
         ms_step = dev_ms / args.steps
         value = world * audio_sec_per_step / (ms_step * 1e-3)
         frames = S * n_chunks * FRAMES_PER_CHUNK
-        nn_flop = S * n_chunks * STEPS_PER_CHUNK * FLOP_PER_FRAME_STEP
+        nn_flop_ref = S * n_chunks * STEPS_PER_CHUNK * FLOP_PER_FRAME_STEP  # what the reference's ORT run executes
+        # what this backend executes: fc1 folded into W1 when the graph has no activation between them (tensor-core
+        # backend), fc2..fc4 only on the 50 rows whose output the reference keeps (NSNet2.zig:188-190)
+        folded = args.nn_mode != "f32" and not wd.get("fc1_relu") and os.environ.get("FVAD_NN_FOLD_FC1", "1") != "0"
+        mac_rec = (MAC_FOLDED_W1 if folded else MAC_FC1 + MAC_GRU_W) + MAC_GRU_W + 2 * MAC_GRU_R
+        nn_flop = 2.0 * S * n_chunks * (STEPS_PER_CHUNK * mac_rec + FRAMES_PER_CHUNK * MAC_TAIL)
+        gru_kernel = "tc_gru_kernel" if os.environ.get("FVAD_GRU_PAIR", "1") == "0" else "tc_gru2_kernel"
         nn_ms = stage[1] / args.steps
         stft_ms = stage[0] / args.steps
         istft_ms = stage[2] / args.steps  # the stage also holds two small carry copies (kilobytes)
@@ -410,12 +473,16 @@ def run_native(args):
             "data": "synthetic", "config": workload_config(args),
             "stage_ms_per_step": {k: float(v) / args.steps for k, v in zip(["stft", "nsnet2", "istft", "vadfft", "vadscan"], stage)},
             "nn_stage_roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
-                         "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,  # a stage of nine kernels; per-kernel traffic below
+                         "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,  # a stage of eight kernels; per-kernel traffic below
+                         "flop_counted": "executed: " + ("fc1 folded into the first GRU input projection (K = 161), " if folded else "")
+                                         + "fc2-fc4 on the 50 kept rows of 54",
+                         "flop_executed": nn_flop, "flop_as_executed_by_reference": float(nn_flop_ref),
+                         "achieved_on_reference_count": nn_flop_ref / (nn_ms * 1e-3) / 1e12 if nn_ms > 0 else 0.0,
                          "peak_source": f"{which} bf16_tflops_sustained"},
-            "roofline": {"kernel": "tc_gru_kernel (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
+            "roofline": {"kernel": gru_kernel + " (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
                                 "bound": "tensor", "achieved": gru_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": gru_tf / tf_peak,
                                 "avg_launch_ms": gru_ms / max(gru_n, 1), "flop_per_launch": gru_flop_total / max(gru_n, 1),
-                                "traffic": ncu_traffic("tc_gru_kernel", S, args.hours, args.sample_rate),
+                                "traffic": ncu_traffic(gru_kernel, S, args.hours, args.sample_rate),
                                 "peak_source": f"{which} bf16_tflops_sustained"},
             "nn_layer_ms_per_step": {k: float(v) / args.steps for k, v in zip(names, layer_ms)},
             "stft_roofline": {"kernel": "stft_kernel", "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
@@ -443,6 +510,10 @@ def run_native(args):
             "gpu_launches": int(launches), "segments_found": int(n_segments), "clocks": clk,
             "host_affinity": host_cpus,
         }
+        if world == 1 and not args.no_48k:
+            del x
+            torch.cuda.empty_cache()
+            out["ref_legal_48k_stereo"] = run_48k_stereo(fv, wd, nn_mode, local, seeds, S, min(args.hours, 0.25), 2)
         # CPU baseline on a bounded sample (N=1 only)
         if world == 1 and not args.no_cpu_baseline:
             if _ORIG_AFFINITY:
@@ -473,6 +544,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=200.0)
     ap.add_argument("--ref-seconds", type=float, default=120.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-48k", action="store_true", help="skip the extra 48 kHz x 2 channel line (N = 1 only)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "native":
         print("bench.py: warning: W < 3 warm-up steps breaks the timing rules", file=sys.stderr)

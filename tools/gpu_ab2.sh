@@ -1,7 +1,7 @@
 #!/bin/bash
 # A/B on one box; prints per-layer NN ms
 for v in "$@"; do
-  env $v python bench.py --steps 2 --warmup 2 --hours 1 --no-cpu-baseline --e2e-steps 1 > gpurun_out/ab2.json 2>gpurun_out/ab2.err
+  env $v python bench.py --steps 2 --warmup 2 --hours 1 --no-cpu-baseline --no-48k --e2e-steps 1 > gpurun_out/ab2.json 2>gpurun_out/ab2.err
   python - <<PY
 import json
 d=json.load(open("gpurun_out/ab2.json"))

@@ -5,7 +5,7 @@ cp $L /tmp/keep.so
 for r in $(seq 1 ${3:-2}); do
 for lib in $1 $2; do
   cp $lib $L
-  python bench.py --steps 2 --warmup 2 --hours 1 --no-cpu-baseline --e2e-steps 1 > gpurun_out/ab2.json 2>gpurun_out/ab2.err
+  python bench.py --steps 2 --warmup 2 --hours 1 --no-cpu-baseline --no-48k --e2e-steps 1 > gpurun_out/ab2.json 2>gpurun_out/ab2.err
   python - <<PY
 import json
 d=json.load(open("gpurun_out/ab2.json"))
