@@ -37,6 +37,8 @@
 // can still share the SM (a GEMM CTA that owns the whole register file cannot start next to them).
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "nn_tc.cuh"
 #include "tc_dev.cuh"
 
@@ -500,7 +502,8 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     // A staging: a whole tile's slabs when that leaves the weight ring six stages.  Timeline: with a buffer fewer the last slab's load starts only when the first
     // buffer has been restaged and lands ~1 000 cycles late; with a ring that holds less than two N-tiles the producer
     // waits for MMA completions and the L2 latency is exposed.
-    const int min_stages = 6;
+    int min_stages = 8;  // (A/B per 20 stream-hours: fc3 5.22 -> 4.84 ms with 9 stages + 3 A buffers instead of 6 + 4; K = 400 layers indifferent)
+    if (const char *e = getenv("FVAD_PAIR_MINSTAGES")) min_stages = atoi(e);  // experiments
     pl.n_abuf = pl.n_slabs < kMaxABuf ? pl.n_slabs : kMaxABuf;
     while (pl.n_abuf > 2 && (kSmemTotal - pl.n_abuf * pl.a_slab_bytes - fixed) / pl.stage_bytes < min_stages) --pl.n_abuf;
     pl.b_off = pl.n_abuf * pl.a_slab_bytes;

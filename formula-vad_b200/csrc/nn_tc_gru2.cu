@@ -211,7 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                 uint4 xn[6];
 #pragma unroll
                 for (int i = 0; i < 6; ++i)
-                    xn[i] = valid ? __ldg(reinterpret_cast<const uint4 *>(xpt + (size_t)(g * 6 + i) * (kTileM * 16))) : make_uint4(0, 0, 0, 0);
+                    xn[i] = valid ? ldg_stream(xpt + (size_t)(g * 6 + i) * (kTileM * 16)) : make_uint4(0, 0, 0, 0);
                 for (int c = g; c < kChunks; c += 2) {
                     uint4 x[6];
 #pragma unroll
@@ -219,7 +219,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                     if (c + 2 < kChunks && valid) {
 #pragma unroll
                         for (int i = 0; i < 6; ++i)
-                            xn[i] = __ldg(reinterpret_cast<const uint4 *>(xpt + (size_t)((c + 2) * 6 + i) * (kTileM * 16)));
+                            xn[i] = ldg_stream(xpt + (size_t)((c + 2) * 6 + i) * (kTileM * 16));
                     }
                     const uint32_t it = step * kChunks + (uint32_t)c;
                     const uint32_t ai = it % kAccs, use = it / kAccs;
