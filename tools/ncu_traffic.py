@@ -1,4 +1,4 @@
-"""profiles/r01_traffic.json from `ncu -i X.ncu-rep --page raw --csv` of the full-size bench workload:
+"""profiles/rNN_traffic.json from `ncu -i X.ncu-rep --page raw --csv` of the full-size bench workload:
 per kernel, DRAM bytes (read + write) of its first launch.  usage: ncu_traffic.py raw.csv streams hours sample_rate chunks_per_stream > out.json"""
 import csv
 import json
