@@ -357,7 +357,7 @@ private:
         if (!tp || gtraced_) return;
         const char *want = getenv("FVAD_GEMM_TRACE_LAYER");
         const Layer *sel = fold_fc1_ ? &gWf_ : &gW_[0];
-        if (want) sel = !strcmp(want, "fc1") ? &fc1_ : !strcmp(want, "W2") ? &gW_[1] : !strcmp(want, "fc2") ? &fc2_ : !strcmp(want, "fc3") ? &fc3_ : &gW_[0];
+        if (want) sel = !strcmp(want, "fc1") ? &fc1_ : !strcmp(want, "W2") ? &gW_[1] : !strcmp(want, "fc2") ? &fc2_ : !strcmp(want, "fc3") ? &fc3_ : sel;
         if (sel != &L) return;
         gtraced_ = true;
         const size_t ne = 5 * 4 * 8 * 32;
