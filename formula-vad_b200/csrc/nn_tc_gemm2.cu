@@ -26,15 +26,17 @@
 //   * two MMA-issuing threads, one per accumulator (even / odd N-tiles): one's barrier round trips, descriptor
 //     arithmetic and commits hide under the other's issue burst (an N = 96 slab of 8 MMAs is 384 tensor cycles,
 //     a lone issuer needs ~450 per slab);
-//   * the epilogue loads the accumulator one 32-column chunk ahead of its arithmetic and hands the accumulator
-//     back as soon as its last chunk sits in registers.
+//   * EIGHT epilogue warps (two sets on alternate 32-column chunks): the epilogue is bound by the dependent-issue
+//     latency of one warp per scheduler (~30 instructions per 8 columns: bias, activation, fp16 pack, 16-byte store),
+//     not by tcgen05.ld (200 B/clk/SM with four warps, 357 with eight: tools/tmemld_bw.cu), so a second warp per
+//     scheduler nearly halves it; the accumulator goes back to the issuer as soon as a warp's last chunk sits in registers.
 //
 // Roles (both CTAs run all of them except the MMA issuers): warp 0 weight producer (TMA), warp 3 A producer
 // (cp.async.bulk), warps 1 and 2 MMA issuers (leader only; commits multicast to both CTAs; warp 2 also owns the TMEM
-// allocation), warps 4..7 epilogue (own 128 rows), warps 8..11 A stagers (staging buffer -> TMEM, tcgen05.st), and
-// for the gains output (NSETS = 2: its scatter is store-latency bound) warps 12..15 as a second epilogue set on
-// alternate 32-column chunks.  The f16 layers stay at 384 threads x <= 128 registers so the VAD scan's one-warp CTAs
-// can still share the SM (a GEMM CTA that owns the whole register file cannot start next to them).
+// allocation), warps 4..7 and 12..15 epilogue (own 128 rows, alternate 32-column chunks), warps 8..11 A stagers
+// (staging buffer -> TMEM, tcgen05.st).  512 threads x <= 112 registers (__maxnreg__): the VAD scan's one-warp CTAs must
+// still fit on the SM (a GEMM CTA that owns the whole register file cannot start next to them: measured, fc3 +60 %).
+// NSETS = 1 (384 threads, loads software-pipelined one chunk ahead) is kept as a template option.
 #include <cuda.h>
 
 #include <cstdlib>
@@ -486,9 +488,8 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     for (int j = 0; j < a.n_tiles; ++j) nt_max = nt_max > a.nt_size[j] ? nt_max : a.nt_size[j];
     if (a.K % 16 || a.K / 2 + 2 * nt_max > 512)
         throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: A tile + two accumulators exceed the 512 TMEM columns");
-    // The epilogue drains accumulators at ~50 B/clk/SM (tcgen05.ld, tools/tmemld_bw.cu) and a K = 400 layer produces
-    // 41 B/clk/SM of them at the full tensor rate: with two buffers every hand-over latency is exposed, a third
-    // decouples the two pipelines.
+    // A third accumulator when the N-tiles leave room for it (not with the N-tiles nn_tc.cu cuts today: measured
+    // per 20 stream-hours, W at N-tiles of 96 x three accumulators 7.4 ms against 144 x two 7.1).
     pl.n_acc = a.K / 2 + 3 * nt_max <= 512 ? 3 : 2;
     pl.nk_total = a.K / 16;
     pl.ks = pair_slab_ksteps(a.K);
