@@ -39,14 +39,18 @@ def test_reference_arm_other_ranks_print_nothing():
 
 def test_traffic_lookup_follows_the_committed_capture():
     b = _bench_module()
-    with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+    # the newest capture that holds a kernel wins (r02 for the kernels of this round, r01 for the one-CTA GRU)
+    with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
         t = json.load(f)
+    with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+        t1 = json.load(f)
     w = t["workload"]
-    for k in ("tc_gru_kernel", "stft_kernel_d1", "istft_stream_kernel"):
+    assert b.ncu_traffic("tc_gru_kernel", w["streams"], w["hours"], w["sample_rate"]) == t1["kernels"]["tc_gru_kernel"]["dram_bytes_per_launch"]
+    for k in ("tc_gru2_kernel", "stft_kernel_d1", "istft_stream_kernel"):
         v = b.ncu_traffic(k, w["streams"], w["hours"], w["sample_rate"])
         assert v == t["kernels"][k]["dram_bytes_per_launch"] and v > 1e9
         # DRAM traffic of a launch stays close to its algorithmic bytes (no wasted re-reads)
     frames = w["streams"] * b.ncu_traffic_chunks("stft_kernel_d1") * b.FRAMES_PER_CHUNK
     assert 0.9 < b.ncu_traffic("stft_kernel_d1", w["streams"], w["hours"], w["sample_rate"]) / (frames * 2280) < 1.1
     assert 0.9 < b.ncu_traffic("istft_stream_kernel", w["streams"], w["hours"], w["sample_rate"]) / (frames * b.ISTFT_BYTES_PER_FRAME) < 1.1
-    assert b.ncu_traffic("tc_gru_kernel", w["streams"] + 1, w["hours"], w["sample_rate"]) is None  # another workload: no figure
+    assert b.ncu_traffic("tc_gru2_kernel", w["streams"] + 1, w["hours"], w["sample_rate"]) is None  # another workload: no figure
