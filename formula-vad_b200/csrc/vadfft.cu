@@ -58,7 +58,7 @@ __device__ __forceinline__ float2 rfft_bin_padded(const float2 *__restrict__ Z, 
 }
 
 template <int D>
-__global__ void __launch_bounds__(kVadThreads, D == 1 ? 2 : 1) vadfft_kernel(VadFftArgs a, const float2 *__restrict__ gT,
+__global__ void __launch_bounds__(kVadThreads, 2) vadfft_kernel(VadFftArgs a, const float2 *__restrict__ gT,
                                                                 const float *__restrict__ ghann, float norm) {
     __shared__ float2 T[1024];
     __shared__ float2 zb[kVadWarps][512 + 32];  // one pad slot per 16: the bit-reversed store (stride 16) spreads over all banks
@@ -106,31 +106,46 @@ __global__ void __launch_bounds__(kVadThreads, D == 1 ? 2 : 1) vadfft_kernel(Vad
             // y16 index 0 of the span sits at +kYLook; (rel + i) is the input-rate offset
             const float *__restrict__ y = a.y16 + (size_t)(s * a.C + ch) * ypitch + kYLook;
             float2 v[16];
+            if (D == 1) {
 #pragma unroll
-            for (int q = 0; q < 16; ++q) {
-                const int n = lane + 32 * q;
-                float e[2];
-                if (D == 1) {
+                for (int q = 0; q < 16; ++q) {
+                    const int n = lane + 32 * q;
                     const float2 t = *reinterpret_cast<const float2 *>(y + rel + 2 * n);  // rel and the row pitch are even
-                    e[0] = t.x; e[1] = t.y;
-                } else {
+                    const float2 hw = hann2[n];
+                    v[q] = make_float2(t.x * hw.x, t.y * hw.y);
+                }
+            } else {
+                // resample.zig:44-59: input-rate position 3m+2 carries y16[m]; 3m and 3m+1 interpolate from y16[m-1] with
+                // frac = (phase+1)/3 in f32.  The frame's 1024 positions draw on y16[m0-1 .. m0+341]: the warp stages that
+                // run in its (not yet used) Z buffer with coalesced loads, then every lane interpolates its 32 positions
+                // from shared memory -- no 64-bit division, no per-sample global loads, no per-sample f32 division.
+                const int rel32 = (int)rel;                                                  // |rel| < 2^31 (a span is < 2^27 samples)
+                const int m0 = rel32 >= 0 ? rel32 / D : -((-rel32 + D - 1) / D);            // floor(rel / D)
+                const int r0 = rel32 - m0 * D;                                               // phase of the frame's first position
+                float *ys = reinterpret_cast<float *>(Z);
+                const int m_hi = kChunk16 * a.K - 1;                                         // last y16 sample of the span
+#pragma unroll
+                for (int i = 0; i < 11; ++i) {
+                    const int m = m0 - 1 + lane + 32 * i;
+                    ys[lane + 32 * i] = m <= m_hi ? y[m] : 0.0f;
+                }
+                __syncwarp();
+                const float f1 = __fdiv_rn(1.0f, (float)D), f2 = __fdiv_rn(2.0f, (float)D);
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const int n = lane + 32 * q;
+                    float e[2];
 #pragma unroll
                     for (int j = 0; j < 2; ++j) {
-                        // resample.zig:44-59: position 3m+2 carries y16[m]; 3m and 3m+1 interpolate from y16[m-1]
-                        const long long p = rel + 2 * n + j;
-                        const long long m = (p >= 0) ? p / D : -((-p + D - 1) / D);
-                        const int ph = (int)(p - m * D);
-                        const float cur = y[m];
-                        if (ph == D - 1) e[j] = cur;
-                        else {
-                            const float prev = y[m - 1];
-                            const float frac = __fdiv_rn((float)(ph + 1), (float)D);
-                            e[j] = fmaf(cur - prev, frac, prev);
-                        }
+                        const int u = r0 + 2 * n + j;      // position relative to 3*m0
+                        const int dm = u / D, ph = u - dm * D;
+                        const float prev = ys[dm], cur = ys[dm + 1];  // y16[m0+dm-1], y16[m0+dm]
+                        e[j] = ph == D - 1 ? cur : fmaf(cur - prev, ph == 0 ? f1 : f2, prev);
                     }
+                    const float2 hw = hann2[n];
+                    v[q] = make_float2(e[0] * hw.x, e[1] * hw.y);
                 }
-                const float2 hw = hann2[n];
-                v[q] = make_float2(e[0] * hw.x, e[1] * hw.y);
+                __syncwarp();  // the staged run is read before the transform's result overwrites it
             }
             warp_cfft_tw<16, false>(v, ftw);
 #pragma unroll
@@ -180,7 +195,7 @@ void launch_vadfft(const VadFftArgs &a, const Tables &t, cudaStream_t s) {
     if (a.n_bands > kMaxBands) throw Error(FVAD_ERR_INVALID_ARGUMENT, "too many distinct speech bands");
     if (a.fft_size != 1024) throw Error(FVAD_ERR_INVALID_FFT_SIZE, "GPU VAD path supports fft_size 1024");
     const long long items = (long long)a.n_frames * a.S;
-    const unsigned grid = (unsigned)std::min<long long>((items + kVadWarps - 1) / kVadWarps, 148 * (a.D == 1 ? 2 : 1));
+    const unsigned grid = (unsigned)std::min<long long>((items + kVadWarps - 1) / kVadWarps, 148 * 2);
     if (a.work_ctr) FVAD_CUDA_CHECK(cudaMemsetAsync(a.work_ctr, 0, sizeof(unsigned long long), s));
     if (a.D == 1) vadfft_kernel<1><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
     else if (a.D == 3) vadfft_kernel<3><<<grid, kVadThreads, 0, s>>>(a, t.T1024, t.hann1024, t.vad_norm);
