@@ -227,6 +227,7 @@ public:
         const int q_total = (total + tc::kTileM - 1) / tc::kTileM;
         const int QB = std::min(q_total, 2 * n_sm_);  // tiles per sub-batch
         if (!sp.feat16) throw Error(FVAD_ERR_INVALID_ARGUMENT, "the tensor-core backend reads the fp16 feature rows");
+        if (const char *e = getenv("FVAD_NN_GATHER")) gather_ = atoi(e) != 0;
         a0_.ensure((size_t)QB * kSteps * tc::tile_bytes(176) / 2);
         if (!fold_fc1_) x1_.ensure((size_t)QB * kSteps * tc::tile_bytes(400) / 2);
         xp_.ensure((size_t)QB * kSteps * tc::tile_bytes(1200) / 2);
@@ -238,12 +239,19 @@ public:
             const int Q = std::min(QB, q_total - q0);
             const __half *a0 = a0_.p;
             tc::PackArgs pa{static_cast<const __half *>(sp.feat16), a0_.p, Q, q0 * tc::kTileM, total, sp.K};
+            // the folded first projection on CTA pairs gathers its 54-row windows from the feature rows itself
+            const bool gather = fold_fc1_ && gWf_.pair && gather_;
             mark(0, s);
-            tc::launch_tc_pack(pa, s);
+            if (!gather) tc::launch_tc_pack(pa, s);
             mark(1, s);
             if (!fold_fc1_) gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
             mark(2, s);
-            if (fold_fc1_) gemm(gWf_, a0, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
+            if (gather) {
+                GemmArgs g = base_args(gWf_, nullptr, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0);
+                g.gather_rows = static_cast<const __half *>(sp.feat16); g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
+                maybe_trace(g, gWf_, s);
+                launch(g, gWf_, s);
+            } else if (fold_fc1_) gemm(gWf_, a0, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             else gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             mark(3, s);
             gru(0, h1_.p, Q, 0, s);
@@ -294,6 +302,9 @@ private:
     int n_sm_ = 148, fc1_relu_ = 0;
     Layer fc1_, gW_[2], gWf_, fc2_, fc3_, fc4_;
     bool fold_fc1_ = false;   // fc1 folded into W1 (gWf_): see the constructor
+    bool gather_ = false;     // FVAD_NN_GATHER=1: the folded projection's A stagers gather the 54-row windows from the feature rows
+                              // themselves (no pack pass).  Parity-green, measured neutral per 20 stream-hours (pack 1.55 -> 0 ms, the
+                              // projection 4.13 -> 5.67: thread-per-row 32-byte loads), so the pack kernel stays the default
     DevBuf<__half> gR_[2], gR2_[2];
     CUtensorMap gRmap_[2];  // TMA view of gR2_ (pair kernel)
     // per-layer CUDA-event timing (events only, no extra synchronisation); FVAD_NN_TIMING=1 prints the lifetime sums

@@ -41,7 +41,10 @@ struct GemmArgs {
     int a_tmem;    // 1: the A tile lives in TMEM (tcgen05.cp + A-from-TMEM MMAs), all shared memory is weight ring; needs
                    //    K/2 + 2*max(nt_size) <= 512 TMEM columns
     int dbg;       // experiments only (FVAD_GEMM_DBG): bit 0 epilogue does no work, bit 1 producer copies nothing
-    int seq0, n_seq, Kchunks;  // scatter: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
+    int seq0, n_seq, Kchunks;  // scatter / gather: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
+    const __half *gather_rows; // pair kernel, K = 176 only: A is not tiles but the fp16 feature rows [SC][4+50*Kchunks][176]; row r of
+                               // M-tile (q, t) is row 50*j + t of stream-channel sc, (sc, j) = divmod(seq0 + 128 q + r, Kchunks) --
+                               // the 54-row windows are gathered by the A stagers themselves (no pack pass); nullptr otherwise
 };
 void launch_tc_gemm(const GemmArgs &a, int n_sm, cudaStream_t s);
 

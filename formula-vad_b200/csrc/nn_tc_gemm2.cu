@@ -85,7 +85,12 @@ struct PairPlan {  // host-computed (launch_tc_gemm2)
     int n_acc;          // accumulators: 3 when 3*acc_cols + K/2 <= 512 (N-tile `work` uses accumulator work % n_acc), else 2; A follows them
 };
 
-template <int ACT, int OUT, int NSETS>
+// GATHER (K = 176, two slabs of 6 + 5 K-steps): the A operand is gathered from the fp16 feature rows by the stager warps
+// (thread = row: 22 16-byte loads per row, issued for the NEXT M-tile as soon as this one is in TMEM, so they fly under a whole
+// M-tile of MMAs), see GemmArgs::gather_rows.  No staging buffers, no A producer: all of shared memory is weight ring.
+constexpr int kGatherKsteps = 11, kGatherKs = 6;
+
+template <int ACT, int OUT, int NSETS, bool GATHER>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS - 1), 1) __maxnreg__(NSETS == 2 ? 112 : 128)
     tc_gemm_pair_kernel(const GemmArgs a, const PairPlan pl, const __grid_constant__ PairMaps maps) {
     constexpr int kThreads = 384 + 128 * (NSETS - 1);
@@ -158,7 +163,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
         }
     } else if (warp == 3) {
         // ===== A producer: this CTA's own M-tile, slab by slab into the staging buffers =====
-        if (elect_one()) {
+        if (!GATHER && elect_one()) {
             uint32_t ab = 0, abph = 0;
             for (int mp = pair0; mp < n_mpairs; mp += pair_stride) {
                 const int mt = 2 * mp + (int)rank;
@@ -246,7 +251,42 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
         const uint32_t tA = tA0 + ((uint32_t)((warp & 3) * 32) << 16);
         const uint32_t a_full_leader = mapa_u32(&sh->a_full[0], 0);
         uint32_t ab = 0, abph = 0, im = 0;
-        for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+        if (GATHER) {
+            uint4 d[2 * kGatherKsteps];  // this thread's row of the current M-tile: 11 K-steps x 32 bytes
+            auto fetch = [&](int mp) {
+                const int mt = 2 * mp + (int)rank;
+                const int q = mt / a.T, t = mt % a.T;
+                const int g = a.seq0 + q * kTileM + row;
+                const bool ok = mt < a.mt_count && g < a.n_seq;
+                const int sc = ok ? g / a.Kchunks : 0, j = ok ? g - sc * a.Kchunks : 0;
+                const uint4 *src = reinterpret_cast<const uint4 *>(a.gather_rows + ((size_t)sc * (kCtx + kFrames * a.Kchunks) + (size_t)kFrames * j + t + a.A_t0) * 176);
+#pragma unroll
+                for (int i = 0; i < 2 * kGatherKsteps; ++i) d[i] = ok ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
+            };
+            if (pair0 < n_mpairs) fetch(pair0);
+            for (int mp = pair0; mp < n_mpairs; mp += pair_stride, ++im) {
+#pragma unroll
+                for (int sl = 0; sl < 2; ++sl) {
+                    mbar_wait(&sh->a_empty[sl], (im & 1) ^ 1);  // the previous M-tile's MMAs over these columns are done
+                    tc_fence_after();
+#pragma unroll
+                    for (int kk = 0; kk < kGatherKs; ++kk) {
+                        const int ks_abs = sl * kGatherKs + kk;
+                        if (ks_abs < kGatherKsteps) {
+                            const uint32_t r[8] = {d[2 * ks_abs].x, d[2 * ks_abs].y, d[2 * ks_abs].z, d[2 * ks_abs].w,
+                                                   d[2 * ks_abs + 1].x, d[2 * ks_abs + 1].y, d[2 * ks_abs + 1].z, d[2 * ks_abs + 1].w};
+                            tmem_st8(tA + (uint32_t)ks_abs * 8u, r);
+                        }
+                    }
+                    tmem_wait_st();
+                    tc_fence_before();
+                    bar_sync(1, 128);
+                    if (warp == 8 && lane == 0) mbar_arrive_addr(a_full_leader + 8u * (uint32_t)sl);
+                }
+                if (mp + pair_stride < n_mpairs) fetch(mp + pair_stride);
+            }
+        }
+        for (int mp = pair0; !GATHER && mp < n_mpairs; mp += pair_stride, ++im) {
             const bool valid = 2 * mp + (int)rank < a.mt_count;
             for (int sl = 0; sl < n_slabs; ++sl) {
                 const int nk = min(ks, pl.nk_total - sl * ks);
@@ -471,14 +511,14 @@ void build_pair_maps(PairMaps &maps, const void *img2, int K, int n_tiles, const
         }
 }
 
-template <int ACT, int OUT, int NSETS>
+template <int ACT, int OUT, int NSETS, bool GATHER = false>
 static void launch_pair_variant(const GemmArgs &a, const PairPlan &pl, const PairMaps &maps, int grid, cudaStream_t s) {
     static bool attr = false;
     if (!attr) {
-        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_pair_kernel<ACT, OUT, NSETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+        FVAD_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_pair_kernel<ACT, OUT, NSETS, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
         attr = true;
     }
-    tc_gemm_pair_kernel<ACT, OUT, NSETS><<<grid, 384 + 128 * (NSETS - 1), pl.smem_bytes, s>>>(a, pl, maps);
+    tc_gemm_pair_kernel<ACT, OUT, NSETS, GATHER><<<grid, 384 + 128 * (NSETS - 1), pl.smem_bytes, s>>>(a, pl, maps);
 }
 
 void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStream_t s) {
@@ -505,7 +545,9 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     // waits for MMA completions and the L2 latency is exposed.
     int min_stages = 8;  // (A/B per 20 stream-hours: fc3 5.22 -> 4.84 ms with 9 stages + 3 A buffers instead of 6 + 4; K = 400 layers indifferent)
     if (const char *e = getenv("FVAD_PAIR_MINSTAGES")) min_stages = atoi(e);  // experiments
-    pl.n_abuf = pl.n_slabs < kMaxABuf ? pl.n_slabs : kMaxABuf;
+    if (a.gather_rows && (a.K != 16 * kGatherKsteps || pl.ks != kGatherKs || pl.n_slabs != 2 || a.out_mode != 0 || a.act != 0))
+        throw Error(FVAD_ERR_INVALID_ARGUMENT, "pair GEMM: the row-gather form is built for the K = 176 projection only");
+    pl.n_abuf = a.gather_rows ? 0 : pl.n_slabs < kMaxABuf ? pl.n_slabs : kMaxABuf;
     while (pl.n_abuf > 2 && (kSmemTotal - pl.n_abuf * pl.a_slab_bytes - fixed) / pl.stage_bytes < min_stages) --pl.n_abuf;
     pl.b_off = pl.n_abuf * pl.a_slab_bytes;
     pl.n_stages = (kSmemTotal - pl.b_off - fixed) / pl.stage_bytes;
@@ -520,7 +562,8 @@ void launch_tc_gemm2(const GemmArgs &a, const PairMaps &maps, int n_sm, cudaStre
     if (a.out_mode == 1) {
         if (a.act != 2) throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: the gains output applies the sigmoid");
         launch_pair_variant<2, 1, 2>(a, pl, maps, grid, s);
-    } else if (a.act == 0) launch_pair_variant<0, 0, 2>(a, pl, maps, grid, s);
+    } else if (a.act == 0 && a.gather_rows) launch_pair_variant<0, 0, 2, true>(a, pl, maps, grid, s);
+    else if (a.act == 0) launch_pair_variant<0, 0, 2>(a, pl, maps, grid, s);
     else if (a.act == 1) launch_pair_variant<1, 0, 2>(a, pl, maps, grid, s);
     else throw Error(FVAD_ERR_INVALID_ARGUMENT, "tc_gemm: unsupported activation/output combination");
     FVAD_LAUNCHED();
