@@ -260,6 +260,49 @@ def workload_config(args):
             "parallelism": f"stream-sharded x{args.gpus}, no collective"}
 
 
+def torch_cpu_nn_standin(wd, calls: int = 20):
+    """the oracle's hand-written GEMV under-represents what onnxruntime/MLAS does on one core, so the NSNet2
+    call of the reference (one [1,54,161] tensor per 0.5 s chunk, ONE intra-op thread: onnxruntime.zig:58,85-88) is also
+    timed with torch's CPU kernels at one thread.  Returns ms per call and the audio-seconds per second one core sustains
+    on the network alone."""
+    import torch
+    H = wd["gru1_R"].shape[1]
+    prev = torch.get_num_threads()
+    torch.set_num_threads(1)
+    try:
+        with torch.no_grad():
+            t = lambda k: torch.from_numpy(np.ascontiguousarray(wd[k]))
+            grus = []
+            for l in (1, 2):
+                g = torch.nn.GRU(H, H, batch_first=True)
+                # ONNX gate order z,r,h -> torch r,z,n
+                perm = torch.cat([torch.arange(H, 2 * H), torch.arange(0, H), torch.arange(2 * H, 3 * H)])
+                g.weight_ih_l0.copy_(t(f"gru{l}_W")[perm]); g.weight_hh_l0.copy_(t(f"gru{l}_R")[perm])
+                g.bias_ih_l0.copy_(t(f"gru{l}_Wb")[perm]); g.bias_hh_l0.copy_(t(f"gru{l}_Rb")[perm])
+                grus.append(g)
+            x = torch.randn(1, STEPS_PER_CHUNK, wd["fc1_w"].shape[1])
+
+            def fwd(x):
+                y = torch.nn.functional.linear(x, t("fc1_w"), t("fc1_b"))
+                if wd.get("fc1_relu"):
+                    y = torch.relu(y)
+                y, _ = grus[0](y)
+                y, _ = grus[1](y)
+                y = torch.relu(torch.nn.functional.linear(y, t("fc2_w"), t("fc2_b")))
+                y = torch.relu(torch.nn.functional.linear(y, t("fc3_w"), t("fc3_b")))
+                return torch.sigmoid(torch.nn.functional.linear(y, t("fc4_w"), t("fc4_b")))
+            for _ in range(3):
+                fwd(x)
+            t0 = time.perf_counter()
+            for _ in range(calls):
+                fwd(x)
+            ms = 1e3 * (time.perf_counter() - t0) / calls
+    finally:
+        torch.set_num_threads(prev)
+    return {"ms_per_call_54x161": ms, "threads": 1, "audio_sec_per_sec_per_core_nn_only": 0.5 / (ms * 1e-3),
+            "what": "torch CPU kernels, one thread, same weights: the reference's onnx_instance.run() per 0.5 s channel-chunk"}
+
+
 def run_48k_stereo(fv, wd, nn_mode, local: int, seeds, streams: int, hours: float, steps: int):
     """The reference-legal shape (VADPipeline.zig:55-58 accepts 48 kHz only; main.zig:135-142 runs 2 channels, i.e. two
     NSNet2 sequences per stream-chunk): device-resident and host-f32 end-to-end realtime factor, audio seconds counted
@@ -522,7 +565,8 @@ def run_native(args):
             audio, times, _ = cpu_pipeline_throughput(fv, wd, sr, cores, args.cpu_seconds)
             out["cpu_baseline"] = {"value": audio / times[0], "unit": "audio-sec/sec", "cores": cores, "kind": "port",
                                    "sample": f"{cores} streams x {args.cpu_seconds:.0f} s, one thread per stream (oracle port of the "
-                                             f"reference pipeline; reference binary unavailable: no zig/onnxruntime on this box)"}
+                                             f"reference pipeline; reference binary unavailable: no zig/onnxruntime on this box)",
+                                   "library_grade_nn": torch_cpu_nn_standin(wd)}
         emit(out)
     gp.close()
     if world > 1:
