@@ -82,6 +82,7 @@ EXPORTS = (
     "fvad_pipeline_segments", "fvad_batch_options_default", "fvad_batch_create", "fvad_batch_destroy",
     "fvad_batch_push", "fvad_batch_push_i16", "fvad_batch_segments", "fvad_batch_tap", "fvad_batch_stats_get",
     "fvad_eval_config_default", "fvad_evaluate", "fvad_batch_evaluate", "fvad_vad_machine_scan",
+    "fvad_vad_machine_scan_noalloc",
 )
 
 
@@ -176,6 +177,7 @@ def lib():
     sig("fvad_batch_evaluate", i32, vp, C.POINTER(EvalSegment), C.POINTER(sz), C.POINTER(EvalConfig), C.POINTER(EvalStats))
     sig("fvad_vad_machine_scan", i32, C.POINTER(VadMachineConfig), sz, sz, sz, c_f32p, c_f32p, sz, sz, vp, C.POINTER(Segment), sz,
         C.POINTER(sz))
+    sig("fvad_vad_machine_scan_noalloc", i32, C.POINTER(VadMachineConfig), sz, sz, sz, vp, vp, sz, vp, vp, sz, vp, vp)
     _lib = L
     return L
 

@@ -255,6 +255,31 @@ FVAD_API int fvad_vad_machine_scan(const fvad_vad_machine_config *cfgs, size_t n
                                    size_t frames_per_launch, uint8_t *met, fvad_segment *segments, size_t max_segments,
                                    size_t *n_segments);
 
+/* ------------------------------------------------------------------------------------------
+ * fvad_vad_machine_scan without device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernels and results as fvad_vad_machine_scan, but:
+ *   - every data pointer is a DEVICE pointer supplied by the caller: d_band_min [n_machines][n_frames], d_ratio [n_frames],
+ *     d_met [n_machines][n_frames] or NULL, d_segments [n_machines][max_segments], d_n_segments [n_machines] (uint64:
+ *     every completed segment, also those beyond max_segments); cfgs is a host array;
+ *   - the operator's scratch (derived machine table, scan state, the three rolling-average rings per machine) is a
+ *     file-scope static __device__ array (formula-vad_b200/csrc/noalloc.cu), ~2.1 MB that every GPU which loads the library
+ *     holds until the process exits.  Limits: n_machines <= FVAD_NOALLOC_MAX_MACHINES and, per machine,
+ *     long + short + ratio window lengths in frames <= FVAD_NOALLOC_MAX_RING (the defaults at 48 kHz need 8 469);
+ *     beyond them the call fails with FVAD_ERR_INVALID_ARGUMENT and a message naming the limit;
+ *   - the call allocates nothing on the device (no cudaMalloc / cudaFree, no allocating library routine): it launches
+ *     three kernels on `cuda_stream` (a cudaStream_t, NULL = the default stream) of the current device and synchronises
+ *     that stream before it returns.
+ * The scratch is shared by every call and keeps the last call's contents; each call re-initialises it before the scan.
+ * Calls that overlap on the GPU (two streams, two host threads) RACE on it: serialise them.
+ * ---------------------------------------------------------------------------------------- */
+#define FVAD_NOALLOC_MAX_MACHINES 16
+#define FVAD_NOALLOC_MAX_RING 16384
+FVAD_API int fvad_vad_machine_scan_noalloc(const fvad_vad_machine_config *cfgs, size_t n_machines, size_t sample_rate,
+                                           size_t fft_size, const float *d_band_min, const float *d_ratio, size_t n_frames,
+                                           uint8_t *d_met, fvad_segment *d_segments, size_t max_segments,
+                                           uint64_t *d_n_segments, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
