@@ -148,10 +148,19 @@ public:
         build_layer(fc1_, w.fc1_w.data(), w.fc1_b.data(), nullptr, H, 161, 176, T{208, 192}, gp);
         for (int l = 0; l < 2; ++l) {
             // xp bias: Wb + Rb for z and r; Wb alone for n (Rb_n is applied inside r*(.), nn_tc_gru.cu)
-            std::vector<float> b(3 * H);
+            // The z and r rows of W, R and their biases are stored HALVED: the gates are sigma(x) = 0.5 + 0.5 tanh(x/2) on the
+            // hardware tanh, and with x/2 coming out of the MMAs directly the epilogue saves a multiply per gate.  Exact: a
+            // power of two commutes with every rounding on the way (fp16 weights, fp32 accumulation, fp16 projections), short
+            // of fp16 subnormals.
+            std::vector<float> b(3 * H), Wh(w.gru_W[l]);
             for (int i = 0; i < 3 * H; ++i) b[(size_t)i] = w.gru_Wb[l][(size_t)i] + (i < 2 * H ? w.gru_Rb[l][(size_t)i] : 0.0f);
+            for (int i = 0; i < 2 * H; ++i) {
+                b[(size_t)i] *= 0.5f;
+                for (int k = 0; k < H; ++k) Wh[(size_t)i * H + k] *= 0.5f;
+            }
+            auto Rh = [&](int src, int k) { return (src < 2 * H ? 0.5f : 1.0f) * w.gru_R[l][(size_t)src * H + k]; };
             gp = (pmask & 2) != 0;
-            build_layer(gW_[l], w.gru_W[l].data(), b.data(), perm.data(), 3 * H, H, H,
+            build_layer(gW_[l], Wh.data(), b.data(), perm.data(), 3 * H, H, H,
                         gp ? T{48, 144, 144, 144, 144, 144, 144, 144, 144}
                            : ts ? T{144, 144, 144, 144, 144, 144, 144, 144, 48} : T{240, 240, 240, 240, 240}, gp);
             // R: 25 chunk images of 48 rows = one "layer" with 25 N-tiles of 48
@@ -161,7 +170,7 @@ public:
                 const int c = p / 48, n = p % 48, src = perm[(size_t)p];
                 uint8_t *base = reinterpret_cast<uint8_t *>(img.data()) + (size_t)c * 48 * H * 2;
                 for (int k = 0; k < H; ++k)
-                    *reinterpret_cast<__half *>(base + tc::tiled_off(n, k, 48)) = __float2half_rn(w.gru_R[l][(size_t)src * H + k]);
+                    *reinterpret_cast<__half *>(base + tc::tiled_off(n, k, 48)) = __float2half_rn(Rh(src, k));
             }
             gR_[l].ensure(img.size());
             FVAD_CUDA_CHECK(cudaMemcpy(gR_[l].p, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
@@ -171,7 +180,7 @@ public:
                 const int c = p / 48, n = p % 48, half = n / 24, src = perm[(size_t)p];
                 uint8_t *base = reinterpret_cast<uint8_t *>(img2.data()) + ((size_t)c * 48 + (size_t)half * 24) * H * 2;
                 for (int k = 0; k < H; ++k)
-                    *reinterpret_cast<__half *>(base + tc::tiled_off(n % 24, k, 24)) = __float2half_rn(w.gru_R[l][(size_t)src * H + k]);
+                    *reinterpret_cast<__half *>(base + tc::tiled_off(n % 24, k, 24)) = __float2half_rn(Rh(src, k));
             }
             gR2_[l].ensure(img2.size());
             FVAD_CUDA_CHECK(cudaMemcpy(gR2_[l].p, img2.data(), img2.size() * sizeof(__half), cudaMemcpyHostToDevice));
@@ -193,11 +202,12 @@ public:
                 const float *wr = w.gru_W[0].data() + (size_t)o * H;
                 double acc_b = (double)w.gru_Wb[0][(size_t)o] + (o < 2 * H ? (double)w.gru_Rb[0][(size_t)o] : 0.0);
                 for (int k = 0; k < H; ++k) acc_b += (double)wr[k] * (double)w.fc1_b[(size_t)k];
-                bf[(size_t)o] = (float)acc_b;
+                const double gs = o < 2 * H ? 0.5 : 1.0;  // z and r rows halved, see above
+                bf[(size_t)o] = (float)(gs * acc_b);
                 for (int i = 0; i < NB; ++i) {
                     double acc = 0.0;
                     for (int k = 0; k < H; ++k) acc += (double)wr[k] * (double)w.fc1_w[(size_t)k * NB + i];
-                    Wf[(size_t)o * NB + i] = (float)acc;
+                    Wf[(size_t)o * NB + i] = (float)(gs * acc);
                 }
             }
             gp = (pmask & 2) != 0;
@@ -328,7 +338,11 @@ private:
         unsigned long long *tr = nullptr;
         const char *tp = getenv("FVAD_GRU_TRACE");
         if (tp && l == 0 && !traced_) { trace_.ensure(54 * 25 * 8); FVAD_CUDA_CHECK(cudaMemsetAsync(trace_.p, 0, 54 * 25 * 8 * 8, s)); tr = trace_.p; }
-        if (pair_) tc::launch_tc_gru2(tc::GruArgs{xp_.p, gR2_[l].p, gRbn_[l].p, hout, Q, t_store_min, tr}, gRmap_[l], n_sm_, s);
+        if (pair_) {
+            tc::GruArgs ga{xp_.p, gR2_[l].p, gRbn_[l].p, hout, Q, t_store_min, tr};
+            if (const char *e = getenv("FVAD_GRU_DBG")) ga.dbg = atoi(e);
+            tc::launch_tc_gru2(ga, gRmap_[l], n_sm_, s);
+        }
         else tc::launch_tc_gru(tc::GruArgs{xp_.p, gR_[l].p, gRbn_[l].p, hout, Q, t_store_min, tr}, n_sm_, s);
         if (tr) {  // debug only: dump CTA 0's timeline of the first GRU launch
             traced_ = true;

@@ -40,7 +40,8 @@ struct GemmArgs {
     unsigned long long *trace;  // debug (FVAD_GEMM_TRACE): CTA 0 logs clock64 for its first 4 M-tiles, nullptr otherwise
     int a_tmem;    // 1: the A tile lives in TMEM (tcgen05.cp + A-from-TMEM MMAs), all shared memory is weight ring; needs
                    //    K/2 + 2*max(nt_size) <= 512 TMEM columns
-    int dbg;       // experiments only (FVAD_GEMM_DBG): bit 0 epilogue does no work, bit 1 producer copies nothing
+    int dbg;       // experiments only (FVAD_GEMM_DBG; results are then wrong): bit 0 epilogue does no work, bit 1 producer copies nothing,
+                   // bit 2 (pair kernel) no C stores
     int seq0, n_seq, Kchunks;  // scatter / gather: first global sequence of tile q = 0, sequences in total, chunks per stream-channel
     const __half *gather_rows; // pair kernel, K = 176 only: A is not tiles but the fp16 feature rows [SC][4+50*Kchunks][176]; row r of
                                // M-tile (q, t) is row 50*j + t of stream-channel sc, (sc, j) = divmod(seq0 + 128 q + r, Kchunks) --
@@ -72,6 +73,9 @@ struct GruArgs {
     __half *hout;
     int Q, t_store_min;
     unsigned long long *trace;  // debug (FVAD_GRU_TRACE): CTA 0 logs clock64 at [step][chunk][event], nullptr otherwise
+    int dbg = 0;                // experiments only (FVAD_GRU_DBG, pair kernel; results are then WRONG, only the time means something):
+                                // 1 no accumulator/h loads from TMEM, 2 no weight copies, 4 no x-projection loads, 8 no h_t stores to HBM,
+                                // 16 no gate arithmetic
 };
 void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
 // CTA-pair version (nn_tc_gru2.cu): Rimg is the split image (per chunk two 24-row halves tiled with R = 24), fetched by TMA

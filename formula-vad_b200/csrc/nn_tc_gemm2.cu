@@ -148,8 +148,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                     const uint32_t both = 2u * (uint32_t)(NH * 16) * (uint32_t)(2 * ks);  // the box is always whole (columns past K are zero-filled)
                     for (int sl = 0; sl < n_slabs; ++sl, ++it) {
                         mbar_wait(&sh->empty[st], ph ^ 1);
-                        if (leader) mbar_expect_tx(&sh->full[st], both);
-                        tma2_load_2d(sB + (size_t)st * pl.stage_bytes, tmap, full_leader + 8u * st, 0, sl * 2 * ks);
+                        if (a.dbg & 2) { if (leader) mbar_arrive(&sh->full[st]); }  // (experiments: no weight copies)
+                        else {
+                            if (leader) mbar_expect_tx(&sh->full[st], both);
+                            tma2_load_2d(sB + (size_t)st * pl.stage_bytes, tmap, full_leader + 8u * st, 0, sl * 2 * ks);
+                        }
                         PAIR_TRACE(0, im, j, sl);
                         if (++st == (uint32_t)n_stages) { st = 0; ph ^= 1; }
                     }
@@ -356,7 +359,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                         act8(r + 8 * gI, col + 8 * gI, v);
                         uint4 o;
                         o.x = pack_h2(v[0], v[1]); o.y = pack_h2(v[2], v[3]); o.z = pack_h2(v[4], v[5]); o.w = pack_h2(v[6], v[7]);
-                        *reinterpret_cast<uint4 *>(Ct + (size_t)((col >> 3) + gI) * (kTileM * 16)) = o;
+                        if (!(a.dbg & 4)) *reinterpret_cast<uint4 *>(Ct + (size_t)((col >> 3) + gI) * (kTileM * 16)) = o;
                     }
                 }
             } else {
@@ -415,7 +418,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384 + 128 * (NSETS -
                 // The loads run one chunk ahead of the arithmetic (tcgen05.wait::ld covers every load issued so far, so the
                 // next chunk's load is issued right after the wait for the current one), and the accumulator goes back to
                 // the MMA issuer as soon as this warp's last chunk sits in registers.
-                const int NTv = valid ? NT : 0;
+                const int NTv = (valid && !(a.dbg & 1)) ? NT : 0;  // (dbg 1, experiments: the epilogue drains nothing)
                 constexpr int kStride = 32 * NSETS;
                 int c = hset * 32;
                 bool released = false;

@@ -47,7 +47,8 @@ __device__ __forceinline__ float tanh_hw(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_hw(0.5f * x), 0.5f); }
+// (the argument arrives HALVED: nn_tc.cu stores the z and r rows of W, R and their biases times 1/2)
+__device__ __forceinline__ float sigmoid_fast(float half_x) { return fmaf(0.5f, tanh_hw(half_x), 0.5f); }
 __device__ __forceinline__ float tanh_fast(float x) { return tanh_hw(x); }
 
 __global__ void __launch_bounds__(kGruThreads, 1) tc_gru_kernel(const GruArgs a) {

@@ -73,8 +73,10 @@ __device__ __forceinline__ float tanh_hw(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_hw(0.5f * x), 0.5f); }
-__device__ __forceinline__ float tanh_fast(float x) { return tanh_hw(x); }
+// Gate arithmetic on packed FP32 pairs (FADD2 / FFMA2: one issue slot for two hidden units).  The arguments of the two
+// sigmoids arrive HALVED (nn_tc.cu stores the z and r rows of W, R and their biases times 1/2), so
+// sigma(x) = 0.5 + 0.5 tanh(x/2) is one packed add, two MUFU.TANH and one packed FMA per pair of units.
+__device__ __forceinline__ float2 tanh2(float2 x) { return make_float2(tanh_hw(x.x), tanh_hw(x.y)); }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
     tc_gru2_kernel(const GruArgs a, int n_pairs_total, const __grid_constant__ CUtensorMap rmap) {
@@ -121,8 +123,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                 for (int t = 0; t < kSteps; ++t)
                     for (int c = 0; c < kChunks; ++c, ++it) {
                         mbar_wait(&sh->empty[st], ph ^ 1);
-                        if (leader) mbar_expect_tx(&sh->full[st], 2 * kHalfBytes);
-                        tma2_load_3d(smem + st * kHalfBytes, &rmap, full_leader + 8u * st, 0, 0, 2 * c + (int)rank);
+                        if (a.dbg & 2) { if (leader) mbar_arrive(&sh->full[st]); }
+                        else {
+                            if (leader) mbar_expect_tx(&sh->full[st], 2 * kHalfBytes);
+                            tma2_load_3d(smem + st * kHalfBytes, &rmap, full_leader + 8u * st, 0, 0, 2 * c + (int)rank);
+                        }
                         if (++st == (uint32_t)kStages) { st = 0; ph ^= 1; }
                     }
             // drain: the leader's multicast commits to this CTA's `empty` barriers must have landed before exit
@@ -211,12 +216,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                 uint4 xn[6];
 #pragma unroll
                 for (int i = 0; i < 6; ++i)
-                    xn[i] = valid ? ldg_stream(xpt + (size_t)(g * 6 + i) * (kTileM * 16)) : make_uint4(0, 0, 0, 0);
+                    xn[i] = (valid && !(a.dbg & 4)) ? ldg_stream(xpt + (size_t)(g * 6 + i) * (kTileM * 16)) : make_uint4(0, 0, 0, 0);
                 for (int c = g; c < kChunks; c += 2) {
                     uint4 x[6];
 #pragma unroll
                     for (int i = 0; i < 6; ++i) x[i] = xn[i];
-                    if (c + 2 < kChunks && valid) {
+                    if (c + 2 < kChunks && valid && !(a.dbg & 4)) {
 #pragma unroll
                         for (int i = 0; i < 6; ++i)
                             xn[i] = ldg_stream(xpt + (size_t)((c + 2) * 6 + i) * (kTileM * 16));
@@ -228,10 +233,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                     tc_fence_after();
                     if (wq == 0 && lane == 0) GRU2_TRACE(3, t, c);
                     uint32_t az[16], ar[16], an[16], ho[8];
-                    tmem_ld16(acc, az);
-                    tmem_ld16(acc + 16, ar);
-                    tmem_ld16(acc + 32, an);
-                    tmem_ld8(th + c * 8, ho);  // h_{t-1} of this row's 16 units: TMEM keeps it untouched for the whole step
+                    if (a.dbg & 1) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { az[i] = ar[i] = an[i] = 0; ho[i & 7] = 0; }
+                    } else {
+                        tmem_ld16(acc, az);
+                        tmem_ld16(acc + 16, ar);
+                        tmem_ld16(acc + 32, an);
+                        tmem_ld8(th + c * 8, ho);  // h_{t-1} of this row's 16 units: TMEM keeps it untouched for the whole step
+                    }
                     tmem_wait_ld();
                     tc_fence_before();
                     __syncwarp();
@@ -248,24 +258,29 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                         rb[4 * i] = v.x; rb[4 * i + 1] = v.y; rb[4 * i + 2] = v.z; rb[4 * i + 3] = v.w;
                     }
                     uint32_t hn[8];
+                    if (a.dbg & 16) {
 #pragma unroll
-                    for (int p = 0; p < 8; ++p) {
-                        const float2 xz = unpack_h2(xw[p]), xr = unpack_h2(xw[8 + p]), xnn = unpack_h2(xw[16 + p]);
-                        const float2 hp = unpack_h2(ho[p]);
-                        const float b0 = rb[2 * p], b1 = rb[2 * p + 1];
-                        const float z0 = sigmoid_fast(xz.x + __uint_as_float(az[2 * p]));
-                        const float z1 = sigmoid_fast(xz.y + __uint_as_float(az[2 * p + 1]));
-                        const float r0 = sigmoid_fast(xr.x + __uint_as_float(ar[2 * p]));
-                        const float r1 = sigmoid_fast(xr.y + __uint_as_float(ar[2 * p + 1]));
-                        const float n0 = tanh_fast(xnn.x + r0 * (__uint_as_float(an[2 * p]) + b0));
-                        const float n1 = tanh_fast(xnn.y + r1 * (__uint_as_float(an[2 * p + 1]) + b1));
-                        const float h0 = n0 + z0 * (hp.x - n0);
-                        const float h1 = n1 + z1 * (hp.y - n1);
-                        hn[p] = pack_h2(h0, h1);
+                        for (int p = 0; p < 8; ++p) hn[p] = xw[p] ^ az[p] ^ ho[p];
+                    } else {
+                        const float2 kHalf = make_float2(0.5f, 0.5f), kNeg = make_float2(-1.0f, -1.0f);
+#pragma unroll
+                        for (int p = 0; p < 8; ++p) {
+                            const float2 xz = unpack_h2(xw[p]), xr = unpack_h2(xw[8 + p]), xnn = unpack_h2(xw[16 + p]);
+                            const float2 hp = unpack_h2(ho[p]);
+                            const float2 az2 = make_float2(__uint_as_float(az[2 * p]), __uint_as_float(az[2 * p + 1]));
+                            const float2 ar2 = make_float2(__uint_as_float(ar[2 * p]), __uint_as_float(ar[2 * p + 1]));
+                            const float2 an2 = make_float2(__uint_as_float(an[2 * p]), __uint_as_float(an[2 * p + 1]));
+                            const float2 b2 = make_float2(rb[2 * p], rb[2 * p + 1]);
+                            const float2 z = __ffma2_rn(tanh2(__fadd2_rn(xz, az2)), kHalf, kHalf);
+                            const float2 r = __ffma2_rn(tanh2(__fadd2_rn(xr, ar2)), kHalf, kHalf);
+                            const float2 n = tanh2(__ffma2_rn(r, __fadd2_rn(an2, b2), xnn));
+                            const float2 h = __ffma2_rn(z, __ffma2_rn(n, kNeg, hp), n);  // n + z (h_{t-1} - n)
+                            hn[p] = pack_h2(h.x, h.y);
+                        }
                     }
                     hrow[c * (kTileM * 2)] = make_uint4(hn[0], hn[1], hn[2], hn[3]);
                     hrow[c * (kTileM * 2) + 1] = make_uint4(hn[4], hn[5], hn[6], hn[7]);
-                    if (store) {
+                    if (store && !(a.dbg & 8)) {
                         uint8_t *p = hot + (size_t)(c * 2) * (kTileM * 16);
                         *reinterpret_cast<uint4 *>(p) = make_uint4(hn[0], hn[1], hn[2], hn[3]);
                         *reinterpret_cast<uint4 *>(p + kTileM * 16) = make_uint4(hn[4], hn[5], hn[6], hn[7]);
