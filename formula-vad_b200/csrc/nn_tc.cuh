@@ -75,7 +75,7 @@ struct GruArgs {
     unsigned long long *trace;  // debug (FVAD_GRU_TRACE): CTA 0 logs clock64 at [step][chunk][event], nullptr otherwise
     int dbg = 0;                // experiments only (FVAD_GRU_DBG, pair kernel; results are then WRONG, only the time means something):
                                 // 1 no accumulator/h loads from TMEM, 2 no weight copies, 4 no x-projection loads, 8 no h_t stores to HBM,
-                                // 16 no gate arithmetic
+                                // 16 no gate arithmetic, 32 gates without MUFU.TANH, 64 MUFU.TANH.F16x2 (profiles/r02_gru_knockouts.txt)
 };
 void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
 // CTA-pair version (nn_tc_gru2.cu): Rimg is the split image (per chunk two 24-row halves tiled with R = 24), fetched by TMA

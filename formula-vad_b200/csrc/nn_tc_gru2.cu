@@ -77,6 +77,13 @@ __device__ __forceinline__ float tanh_hw(float x) {
 // sigmoids arrive HALVED (nn_tc.cu stores the z and r rows of W, R and their biases times 1/2), so
 // sigma(x) = 0.5 + 0.5 tanh(x/2) is one packed add, two MUFU.TANH and one packed FMA per pair of units.
 __device__ __forceinline__ float2 tanh2(float2 x) { return make_float2(tanh_hw(x.x), tanh_hw(x.y)); }
+// experiments (FVAD_GRU_DBG 32 / 64): no MUFU at all (wrong results) / one MUFU.TANH.F16x2 for the pair (fp16 gate precision)
+__device__ __forceinline__ float2 tanh2_none(float2 x) { return make_float2(x.x * 0.25f, x.y * 0.25f); }
+__device__ __forceinline__ float2 tanh2_h2(float2 x) {
+    uint32_t u = pack_h2(x.x, x.y), y;
+    asm("tanh.approx.f16x2 %0, %1;" : "=r"(y) : "r"(u));
+    return unpack_h2(y);
+}
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
     tc_gru2_kernel(const GruArgs a, int n_pairs_total, const __grid_constant__ CUtensorMap rmap) {
@@ -263,20 +270,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGru2Threads, 1)
                         for (int p = 0; p < 8; ++p) hn[p] = xw[p] ^ az[p] ^ ho[p];
                     } else {
                         const float2 kHalf = make_float2(0.5f, 0.5f), kNeg = make_float2(-1.0f, -1.0f);
+                        auto gates = [&](auto th) {
 #pragma unroll
-                        for (int p = 0; p < 8; ++p) {
-                            const float2 xz = unpack_h2(xw[p]), xr = unpack_h2(xw[8 + p]), xnn = unpack_h2(xw[16 + p]);
-                            const float2 hp = unpack_h2(ho[p]);
-                            const float2 az2 = make_float2(__uint_as_float(az[2 * p]), __uint_as_float(az[2 * p + 1]));
-                            const float2 ar2 = make_float2(__uint_as_float(ar[2 * p]), __uint_as_float(ar[2 * p + 1]));
-                            const float2 an2 = make_float2(__uint_as_float(an[2 * p]), __uint_as_float(an[2 * p + 1]));
-                            const float2 b2 = make_float2(rb[2 * p], rb[2 * p + 1]);
-                            const float2 z = __ffma2_rn(tanh2(__fadd2_rn(xz, az2)), kHalf, kHalf);
-                            const float2 r = __ffma2_rn(tanh2(__fadd2_rn(xr, ar2)), kHalf, kHalf);
-                            const float2 n = tanh2(__ffma2_rn(r, __fadd2_rn(an2, b2), xnn));
-                            const float2 h = __ffma2_rn(z, __ffma2_rn(n, kNeg, hp), n);  // n + z (h_{t-1} - n)
-                            hn[p] = pack_h2(h.x, h.y);
-                        }
+                            for (int p = 0; p < 8; ++p) {
+                                const float2 xz = unpack_h2(xw[p]), xr = unpack_h2(xw[8 + p]), xnn = unpack_h2(xw[16 + p]);
+                                const float2 hp = unpack_h2(ho[p]);
+                                const float2 az2 = make_float2(__uint_as_float(az[2 * p]), __uint_as_float(az[2 * p + 1]));
+                                const float2 ar2 = make_float2(__uint_as_float(ar[2 * p]), __uint_as_float(ar[2 * p + 1]));
+                                const float2 an2 = make_float2(__uint_as_float(an[2 * p]), __uint_as_float(an[2 * p + 1]));
+                                const float2 b2 = make_float2(rb[2 * p], rb[2 * p + 1]);
+                                const float2 z = __ffma2_rn(th(__fadd2_rn(xz, az2)), kHalf, kHalf);
+                                const float2 r = __ffma2_rn(th(__fadd2_rn(xr, ar2)), kHalf, kHalf);
+                                const float2 n = th(__ffma2_rn(r, __fadd2_rn(an2, b2), xnn));
+                                const float2 h = __ffma2_rn(z, __ffma2_rn(n, kNeg, hp), n);  // n + z (h_{t-1} - n)
+                                hn[p] = pack_h2(h.x, h.y);
+                            }
+                        };
+                        if (a.dbg & 32) gates([](float2 x) { return tanh2_none(x); });
+                        else if (a.dbg & 64) gates([](float2 x) { return tanh2_h2(x); });
+                        else gates([](float2 x) { return tanh2(x); });
                     }
                     hrow[c * (kTileM * 2)] = make_uint4(hn[0], hn[1], hn[2], hn[3]);
                     hrow[c * (kTileM * 2) + 1] = make_uint4(hn[4], hn[5], hn[6], hn[7]);
