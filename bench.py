@@ -493,6 +493,8 @@ def run_native(args):
         mac_rec = (MAC_FOLDED_W1 if folded else MAC_FC1 + MAC_GRU_W) + MAC_GRU_W + 2 * MAC_GRU_R
         nn_flop = 2.0 * S * n_chunks * (STEPS_PER_CHUNK * mac_rec + FRAMES_PER_CHUNK * MAC_TAIL)
         gru_kernel = "tc_gru_kernel" if os.environ.get("FVAD_GRU_PAIR", "1") == "0" else "tc_gru2_kernel"
+        # the first GRU layer with its (folded) input projection fused in (nn_tc_gru3.cu) is then the dominant kernel
+        fused = folded and gru_kernel == "tc_gru2_kernel" and os.environ.get("FVAD_GRU_FUSE", "1") != "0"
         nn_ms = stage[1] / args.steps
         stft_ms = stage[0] / args.steps
         istft_ms = stage[2] / args.steps  # the stage also holds two small carry copies (kilobytes)
@@ -501,8 +503,13 @@ def run_native(args):
         ach_gbs = sb / (stft_ms * 1e-3) / 1e9 if stft_ms > 0 else 0.0
         # dominant kernel: one GRU layer launch (tc_gru_kernel; two layers, identical shapes).  Algorithmic flops of a
         # launch = its share of S*n_chunks sequences x 54 steps x 2*480000 (R.h of the layer).
-        gru_ms, gru_n = layer_ms[3] + layer_ms[5], layer_n[3] + layer_n[5]
-        gru_flop_total = 2.0 * args.steps * S * n_chunks * STEPS_PER_CHUNK * 2 * 480_000
+        if fused:  # one launch = R.h of layer 1 + the folded projection (161 x 1200) over all 54 steps of its tiles
+            gru_kernel = "tc_gru3_kernel"
+            gru_ms, gru_n = layer_ms[3], layer_n[3]
+            gru_flop_total = 2.0 * args.steps * S * n_chunks * STEPS_PER_CHUNK * (MAC_GRU_R + MAC_FOLDED_W1)
+        else:
+            gru_ms, gru_n = layer_ms[3] + layer_ms[5], layer_n[3] + layer_n[5]
+            gru_flop_total = 2.0 * args.steps * S * n_chunks * STEPS_PER_CHUNK * 2 * MAC_GRU_R
         gru_tf = gru_flop_total / (gru_ms * 1e-3) / 1e12 if gru_ms > 0 else 0.0
         names = fv.capi.NN_LAYERS
         kc = ncu_traffic_chunks("stft_kernel_d1")  # algorithmic bytes of the launch the ncu traffic figure belongs to
@@ -517,12 +524,14 @@ def run_native(args):
             "stage_ms_per_step": {k: float(v) / args.steps for k, v in zip(["stft", "nsnet2", "istft", "vadfft", "vadscan"], stage)},
             "nn_stage_roofline": {"kernel": "nsnet2 (GEMMs + 2x54-step GRU)", "bound": "tensor", "achieved": ach_tf, "peak": tf_peak,
                          "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,  # a stage of eight kernels; per-kernel traffic below
-                         "flop_counted": "executed: " + ("fc1 folded into the first GRU input projection (K = 161), " if folded else "")
+                         "flop_counted": "executed: " + ("fc1 folded into the first GRU input projection (K = 161)"
+                                                         + (", itself fused into the first GRU kernel, " if fused else ", ") if folded else "")
                                          + "fc2-fc4 on the 50 kept rows of 54",
                          "flop_executed": nn_flop, "flop_as_executed_by_reference": float(nn_flop_ref),
                          "achieved_on_reference_count": nn_flop_ref / (nn_ms * 1e-3) / 1e12 if nn_ms > 0 else 0.0,
                          "peak_source": f"{which} bf16_tflops_sustained"},
-            "roofline": {"kernel": gru_kernel + " (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps)),
+            "roofline": {"kernel": gru_kernel + (" (dominant: first GRU layer + its input projection, %d launches per step)" % int(gru_n / max(1, args.steps))
+                                                 if fused else " (dominant: 2 layers x %d launches per step)" % int(gru_n / max(1, 2 * args.steps))),
                                 "bound": "tensor", "achieved": gru_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": gru_tf / tf_peak,
                                 "avg_launch_ms": gru_ms / max(gru_n, 1), "flop_per_launch": gru_flop_total / max(gru_n, 1),
                                 "traffic": ncu_traffic(gru_kernel, S, args.hours, args.sample_rate),

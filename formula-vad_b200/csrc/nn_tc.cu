@@ -216,6 +216,40 @@ public:
             build_layer(gWf_, Wf.data(), bf.data(), perm.data(), 3 * H, NB, 176,
                         gp ? T{48, 128, 128, 128, 128, 128, 128, 128, 128, 128} : T{144, 144, 144, 144, 144, 144, 144, 144, 48}, gp);
             gWf_.a_tmem = ts ? 1 : 0;
+            // Images of the fused first layer (nn_tc_gru3.cu): per chunk c two halves of 24 rows tiled with R = 24.
+            //   R: rows [n z r] of units 16c..16c+15 (z, r halved), K = 400;
+            //   W: rows [z r n] of the folded projection (z, r halved), K = 176, bias as fp16 hi + lo in columns 161, 162.
+            fuse_ = pair_;
+            if (const char *e = getenv("FVAD_GRU_FUSE")) fuse_ = fuse_ && atoi(e) != 0;
+            if (fuse_) {
+                std::vector<__half> rimg((size_t)3 * H * H, __float2half(0.0f)), wimg((size_t)3 * H * 176, __float2half(0.0f));
+                for (int c = 0; c < 25; ++c)
+                    for (int n = 0; n < 48; ++n) {
+                        const int u = n % 16, half = n / 24, nr = n % 24;
+                        {   // R row n of the chunk: gate order n, z, r
+                            const int gate = n / 16 == 0 ? 2 : n / 16 - 1;  // ONNX gate index: z 0, r 1, n 2
+                            const int src = gate * H + 16 * c + u;
+                            uint8_t *base = reinterpret_cast<uint8_t *>(rimg.data()) + ((size_t)c * 48 + (size_t)half * 24) * H * 2;
+                            const float gs = gate < 2 ? 0.5f : 1.0f;
+                            for (int k = 0; k < H; ++k)
+                                *reinterpret_cast<__half *>(base + tc::tiled_off(nr, k, 24)) = __float2half_rn(gs * w.gru_R[0][(size_t)src * H + k]);
+                        }
+                        {   // W row n of the chunk: gate order z, r, n (Wf / bf carry the halving already)
+                            const int src = (n / 16) * H + 16 * c + u;
+                            uint8_t *base = reinterpret_cast<uint8_t *>(wimg.data()) + ((size_t)c * 48 + (size_t)half * 24) * 176 * 2;
+                            for (int k = 0; k < NB; ++k)
+                                *reinterpret_cast<__half *>(base + tc::tiled_off(nr, k, 24)) = __float2half_rn(Wf[(size_t)src * NB + k]);
+                            const __half hi = __float2half_rn(bf[(size_t)src]);
+                            *reinterpret_cast<__half *>(base + tc::tiled_off(nr, 161, 24)) = hi;
+                            *reinterpret_cast<__half *>(base + tc::tiled_off(nr, 162, 24)) = __float2half_rn(bf[(size_t)src] - __half2float(hi));
+                        }
+                    }
+                gR3_.ensure(rimg.size());
+                gW3_.ensure(wimg.size());
+                FVAD_CUDA_CHECK(cudaMemcpy(gR3_.p, rimg.data(), rimg.size() * sizeof(__half), cudaMemcpyHostToDevice));
+                FVAD_CUDA_CHECK(cudaMemcpy(gW3_.p, wimg.data(), wimg.size() * sizeof(__half), cudaMemcpyHostToDevice));
+                tc::build_gru3_maps(gR3map_, gW3map_, gR3_.p, gW3_.p);
+            }
         }
         gp = (pmask & 4) != 0;
         build_layer(fc2_, w.fc2_w.data(), w.fc2_b.data(), nullptr, 600, H, H, gp ? T{112, 112, 128, 128, 128} : T{208, 208, 192}, gp);
@@ -250,13 +284,15 @@ public:
             const __half *a0 = a0_.p;
             tc::PackArgs pa{static_cast<const __half *>(sp.feat16), a0_.p, Q, q0 * tc::kTileM, total, sp.K};
             // the folded first projection on CTA pairs gathers its 54-row windows from the feature rows itself
-            const bool gather = fold_fc1_ && gWf_.pair && gather_;
+            const bool fused = fold_fc1_ && fuse_;  // first GRU layer with its input projection fused in: no pack, no projection GEMM
+            const bool gather = !fused && fold_fc1_ && gWf_.pair && gather_;
             mark(0, s);
-            if (!gather) tc::launch_tc_pack(pa, s);
+            if (!gather && !fused) tc::launch_tc_pack(pa, s);
             mark(1, s);
             if (!fold_fc1_) gemm(fc1_, a0, x1_.p, Q, kSteps, kSteps, 0, kSteps, 0, fc1_relu_ ? 1 : 0, s);
             mark(2, s);
-            if (gather) {
+            if (fused) {
+            } else if (gather) {
                 GemmArgs g = base_args(gWf_, nullptr, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0);
                 g.gather_rows = static_cast<const __half *>(sp.feat16); g.seq0 = q0 * tc::kTileM; g.n_seq = total; g.Kchunks = sp.K;
                 maybe_trace(g, gWf_, s);
@@ -264,6 +300,10 @@ public:
             } else if (fold_fc1_) gemm(gWf_, a0, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             else gemm(gW_[0], x1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
             mark(3, s);
+            if (fused) {
+                tc::Gru3Args ga{static_cast<const __half *>(sp.feat16), gRbn_[0].p, h1_.p, Q, 0, q0 * tc::kTileM, total, sp.K};
+                tc::launch_tc_gru3(ga, gR3map_, gW3map_, n_sm_, s);
+            } else
             gru(0, h1_.p, Q, 0, s);
             mark(4, s);
             gemm(gW_[1], h1_.p, xp_.p, Q, kSteps, kSteps, 0, kSteps, 0, 0, s);
@@ -312,6 +352,9 @@ private:
     int n_sm_ = 148, fc1_relu_ = 0;
     Layer fc1_, gW_[2], gWf_, fc2_, fc3_, fc4_;
     bool fold_fc1_ = false;   // fc1 folded into W1 (gWf_): see the constructor
+    bool fuse_ = false;       // ... and that projection fused into the first GRU kernel (nn_tc_gru3.cu; FVAD_GRU_FUSE=0: separate kernels)
+    DevBuf<__half> gR3_, gW3_;
+    CUtensorMap gR3map_, gW3map_;
     bool gather_ = false;     // FVAD_NN_GATHER=1: the folded projection's A stagers gather the 54-row windows from the feature rows
                               // themselves (no pack pass).  Parity-green, measured neutral per 20 stream-hours (pack 1.55 -> 0 ms, the
                               // projection 4.13 -> 5.67: thread-per-row 32-byte loads), so the pack kernel stays the default

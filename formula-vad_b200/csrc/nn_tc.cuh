@@ -83,6 +83,20 @@ void launch_tc_gru(const GruArgs &a, int n_sm, cudaStream_t s);
 void build_gru_pair_map(CUtensorMap &rmap, const void *Rimg2);
 void launch_tc_gru2(const GruArgs &a, const CUtensorMap &rmap, int n_sm, cudaStream_t s);
 
+// First GRU layer with the (fc1-folded) input projection fused in (nn_tc_gru3.cu): reads the fp16 feature rows directly.
+//   feat16: [SC][4+50*Kchunks][176]; row r of tile q is sequence seq0 + 128 q + r = (sc, j) by divmod Kchunks, its 54-row
+//           window starts at row 50 j of stream-channel sc
+//   Rimg3 / Wimg3 (through the tensor maps of build_gru3_maps): per chunk two 24-row halves; R rows in [n z r] order over
+//           K = 400, folded W rows in [z r n] order over K = 176 with the bias as an fp16 hi + lo pair in columns 161, 162
+struct Gru3Args {
+    const __half *feat16;
+    const float *rbn;
+    __half *hout;
+    int Q, t_store_min, seq0, n_seq, Kchunks;
+};
+void build_gru3_maps(CUtensorMap &rmap, CUtensorMap &wmap, const void *Rimg3, const void *Wimg3);
+void launch_tc_gru3(const Gru3Args &a, const CUtensorMap &rmap, const CUtensorMap &wmap, int n_sm, cudaStream_t s);
+
 // feature rows fp16 [SC][4+50K][176] -> fp16 tiles [q][54] of 176 columns for sequences seq0 .. seq0+128*Q-1
 struct PackArgs {
     const __half *feat16;
