@@ -10,10 +10,10 @@ KRE='regex:stft|vadfft|vadscan|tc_|copy_rows|i16_to|upsample|eval_|init_scan|gem
 $SMALL > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KRE" -c 400 --csv --log-file gpurun_out/r02_launches.csv $SMALL > gpurun_out/ncu_launches.log 2>&1
 $SMALL > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k 'regex:tc_gru|tc_gemm|tc_pack|stft_kernel|istft_|vadfft_kernel|vadscan' -c 13 -o gpurun_out/r02_prof_small $SMALL > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k 'regex:tc_gru|tc_gemm|tc_pack|stft_kernel|istft_|vadfft_kernel|vadscan' -c 11 -o gpurun_out/r02_prof_small $SMALL > gpurun_out/ncu_full.log 2>&1
 ncu -i gpurun_out/r02_prof_small.ncu-rep --page raw --csv > gpurun_out/r02_prof_small_raw.csv 2>/dev/null
 FULL="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-48k --e2e-steps 1"
-ncu --set full --clock-control none -k 'regex:tc_gru2_kernel|stft_kernel_d1|istft_stream|tc_gemm_pair_kernel' -c 9 -o gpurun_out/r02_prof_fullsize $FULL > gpurun_out/ncu_fullsize.log 2>&1
+ncu --set full --clock-control none -k 'regex:tc_gru3_kernel|tc_gru2_kernel|stft_kernel_d1|istft_stream|tc_gemm_pair_kernel' -c 8 -o gpurun_out/r02_prof_fullsize $FULL > gpurun_out/ncu_fullsize.log 2>&1
 ncu -i gpurun_out/r02_prof_fullsize.ncu-rep --page raw --csv > gpurun_out/r02_prof_fullsize_raw.csv 2>/dev/null
 tail -3 gpurun_out/r02_pytest_gpu.log; tail -2 gpurun_out/ncu_full.log | cut -c1-200; tail -2 gpurun_out/ncu_fullsize.log | cut -c1-200
 python -c "
