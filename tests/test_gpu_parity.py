@@ -307,3 +307,35 @@ def test_tensor_core_mode_on_other_weight_draws(fv, po, seed, fc1_gain, fc1_relu
     _, _, met = op.frames()
     assert (gp.tap(fv.capi.TAP_MET)[0] == met).mean() >= 0.999
     gp.close()
+
+
+@pytest.mark.parametrize("env", [
+    {},                                                     # default: pair GEMMs, fc1 folded, first GRU layer fused with its projection
+    {"FVAD_GRU_FUSE": "0"},                                 # projection GEMM + pair GRU as two kernels
+    {"FVAD_GRU_FUSE": "0", "FVAD_NN_GATHER": "1"},          # ... with the projection gathering its rows itself (no pack kernel)
+    {"FVAD_NN_FOLD_FC1": "0"},                              # fc1 and the projection as separate layers
+    {"FVAD_GRU_PAIR": "0"},                                 # one-CTA GRU kernel
+    {"FVAD_GRU_PAIR": "0", "FVAD_GEMM_PAIR": "0"},          # round 1's one-CTA kernels throughout
+], ids=lambda e: ",".join(f"{k[5:]}={v}" for k, v in e.items()) or "default")
+def test_every_tensor_core_kernel_variant_meets_the_gain_gate(fv, po, wd, env, monkeypatch):
+    """The A/B variants of the tensor-core backend stay selectable by environment (read when a pipeline is created): each
+    of them must meet the same gates as the default path -- gains within 1e-4 of the oracle's largest gain, every VAD
+    decision equal -- on two streams at once (tile rows from different streams, a partial last tile)."""
+    for k in ("FVAD_GRU_FUSE", "FVAD_NN_GATHER", "FVAD_NN_FOLD_FC1", "FVAD_GRU_PAIR", "FVAD_GEMM_PAIR"):
+        monkeypatch.delenv(k, raising=False)
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    xs = [fv.synth.onboard_stream(40 + s, 17.0, 16000, 1)[0] for s in range(2)]
+    x = np.concatenate(xs, axis=0)
+    gp = fv.BatchPipeline(2, 16000, 1, wd, nn_mode=fv.capi.NN_TC_F16, keep_taps=True)
+    gp.push(x)
+    g_gain, g_met = gp.tap(fv.capi.TAP_GAINS), gp.tap(fv.capi.TAP_MET)
+    gp.close()
+    for s in range(2):
+        op = po.Pipeline(wd, 16000, 1, keep_denoised=True, keep_nn=True)
+        op.push_samples(xs[s])
+        _, gain, _ = op.nn_taps()
+        _, _, met = op.frames()
+        err = np.abs(g_gain[s] - gain).max() / np.abs(gain).max()
+        assert err < 1e-4, (env, s, err)
+        assert (g_met[s] == met).mean() >= 0.999
