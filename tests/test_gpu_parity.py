@@ -339,3 +339,31 @@ def test_every_tensor_core_kernel_variant_meets_the_gain_gate(fv, po, wd, env, m
         err = np.abs(g_gain[s] - gain).max() / np.abs(gain).max()
         assert err < 1e-4, (env, s, err)
         assert (g_met[s] == met).mean() >= 0.999
+
+
+def test_real_nsnet2_weights_if_present(fv, po, tmp_path):
+    """The shipped nsnet2-20ms-baseline.onnx is absent from the reference snapshot (.MISSING_LARGE_BLOBS), so every other
+    test runs on seeded weights of its shapes.  Where the file IS present ($FVAD_NSNET2_ONNX, or data/ next to the repo
+    root), import it with tools/onnx_to_blob.py and hold the tensor-core mode to the same gates on it: gains within 1e-4
+    of the oracle's f32 network (relative to the largest gain), VAD decisions >= 99.9 % equal."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cands = [os.environ.get("FVAD_NSNET2_ONNX", ""), os.path.join(root, "data", "nsnet2-20ms-baseline.onnx")]
+    path = next((c for c in cands if c and os.path.exists(c)), None)
+    if path is None:
+        pytest.skip("no nsnet2-20ms-baseline.onnx on this box (set FVAD_NSNET2_ONNX): parity on the real weights stays unpinned")
+    spec = importlib.util.spec_from_file_location("onnx_to_blob", os.path.join(root, "tools", "onnx_to_blob.py"))
+    o2b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(o2b)
+    wd = o2b.convert(path, str(tmp_path / "real.fvadns2"))
+    x, op, gp = _run_both(fv, po, wd, 16000, 1, 31.0, seed=3, nn_mode=fv.capi.NN_TC_F16)
+    op.push_samples(x)
+    gp.push(x)
+    _, gain, _ = op.nn_taps()
+    err = np.abs(gp.tap(fv.capi.TAP_GAINS)[0] - gain).max() / np.abs(gain).max()
+    _, _, met = op.frames()
+    agree = (gp.tap(fv.capi.TAP_MET)[0] == met).mean()
+    gp.close()
+    print(f"real weights ({path}): f16 gains rel-to-max {err:.3e}, decisions agree {agree:.5f}")
+    assert err < 1e-4 and agree >= 0.999
