@@ -19,7 +19,7 @@ def test_library_sass_is_tcgen05_and_tma():
     for mnemonic in ("UTCHMMA", "UTCHMMA.2CTA", "LDTM", "STTM", "UBLKCP", "UTMALDG"):
         assert mnemonic in sass, mnemonic
     # the kernels that carry them
-    for kernel in ("tc_gemm_pair_kernel", "tc_gru2_kernel", "tc_gemm_kernel", "tc_gru_kernel", "stft_kernel_d1", "istft_stream_kernel",
+    for kernel in ("tc_gemm_pair_kernel", "tc_gru3_kernel", "tc_gru2_kernel", "tc_gemm_kernel", "tc_gru_kernel", "stft_kernel_d1", "istft_stream_kernel",
                    "vadfft_kernel", "vadscan_warp_kernel", "eval_batch_kernel"):
         assert kernel in sass, kernel
     assert " HMMA" not in sass and "HGMMA" not in sass  # no mma.sync / wgmma fallbacks
